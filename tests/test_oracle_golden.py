@@ -1,0 +1,138 @@
+"""Pin the Python oracle against the reference crate's own known-answer vectors.
+
+Fixture: tests/golden/reference_vectors.json (made by tests/golden/extract_golden.py from
+/root/reference; provenance file:line is stored inside the fixture).
+"""
+from oracle import bn254_ref as o
+
+
+def _fq12(dec):
+    c = [int(x) for x in dec]
+    return (((c[0], c[1]), (c[2], c[3]), (c[4], c[5])), ((c[6], c[7]), (c[8], c[9]), (c[10], c[11])))
+
+
+def _fq2(dec):
+    return (int(dec[0]), int(dec[1]))
+
+
+def test_str_vectors(golden):
+    # src/fields/mod.rs:67-81
+    assert int(golden["test_str"]["fr_minus_one"]) == o.R_ORDER - 1
+    assert int(golden["test_str"]["fq_minus_one"]) == o.Q - 1
+
+
+def test_naf_table(golden):
+    assert golden["ate_loop_count_naf"]["digits"] == o.ATE_LOOP_COUNT_NAF
+
+
+def test_montgomery_literals(golden):
+    """Constants the oracle derives from q, r, xi equal the reference's inline Montgomery literals."""
+    m = golden["montgomery_literals"]
+    fm = o.fq_from_mont
+    assert int(m["fq"]["modulus"]) == o.Q and int(m["fr"]["modulus"]) == o.R_ORDER
+    assert int(m["fq"]["one"]) == o.MONT_R % o.Q and int(m["fr"]["one"]) == o.MONT_R % o.R_ORDER
+    assert int(m["fq"]["rsquared"]) == pow(o.MONT_R, 2, o.Q) and int(m["fr"]["rsquared"]) == pow(o.MONT_R, 2, o.R_ORDER)
+    assert int(m["fq"]["rcubed"]) == pow(o.MONT_R, 3, o.Q) and int(m["fr"]["rcubed"]) == pow(o.MONT_R, 3, o.R_ORDER)
+    assert int(m["fq"]["inv128"]) == (-pow(o.Q, -1, 1 << 128)) % (1 << 128)
+    assert int(m["fr"]["inv128"]) == (-pow(o.R_ORDER, -1, 1 << 128)) % (1 << 128)
+    assert int(m["bn_u"]) == o.BN_U
+    assert fm(int(m["fq_non_residue"])) == o.Q - 1
+    assert tuple(fm(int(x)) for x in m["fq2_nonresidue"]) == o.XI
+    assert fm(int(m["two_inv"])) == o.TWO_INV
+    assert fm(int(m["g1_one_y"])) == o.G1_ONE[1] and fm(int(m["g1_coeff_b"])) == o.G1_B
+    assert tuple(fm(int(x)) for x in m["g2_one"]["x"]) == o.G2_ONE[0]
+    assert tuple(fm(int(x)) for x in m["g2_one"]["y"]) == o.G2_ONE[1]
+    assert tuple(fm(int(x)) for x in m["g2_coeff_b"]) == o.G2_B
+    assert tuple(fm(int(x)) for x in m["twist_mul_by_q_x"]) == o.TWIST_MUL_BY_Q_X
+    assert tuple(fm(int(x)) for x in m["twist_mul_by_q_y"]) == o.TWIST_MUL_BY_Q_Y
+    for k in ("1", "2", "3"):
+        assert tuple(fm(int(x)) for x in m["fq6_frobenius_c1"][k]) == o.FQ6_FROB_C1[int(k)]
+        assert tuple(fm(int(x)) for x in m["fq6_frobenius_c2"][k]) == o.FQ6_FROB_C2[int(k)]
+        assert tuple(fm(int(x)) for x in m["fq12_frobenius_c1"][k]) == o.FQ12_FROB_C1[int(k)]
+
+
+def test_generators_on_curve(golden):
+    assert o.affine_on_curve(o.FQ_OPS, o.G1_B, o.G1_ONE[0], o.G1_ONE[1])
+    assert o.affine_on_curve(o.FQ2_OPS, o.G2_B, o.G2_ONE[0], o.G2_ONE[1])
+    pp = golden["predefined_pair"]
+    assert (int(pp["g1"][0]), int(pp["g1"][1])) == o.G1_ONE[:2]
+    assert _fq2(pp["g2_x"]) == o.G2_ONE[0] and _fq2(pp["g2_y"]) == o.G2_ONE[1]
+
+
+def test_fq12_test_vector(golden):
+    # src/fields/mod.rs:93-227
+    v = golden["fq12_test_vector"]
+    start = _fq12(v["start"])
+    nxt = start
+    for _ in range(100):
+        nxt = o.fq12_mul(nxt, start)
+    cpy = nxt
+    for _ in range(10):
+        nxt = o.fq12_sqr(nxt)
+    for _ in range(10):
+        nxt = o.fq12_add(nxt, start)
+        nxt = o.fq12_sub(nxt, cpy)
+        nxt = o.fq12_neg(nxt)
+    nxt = o.fq12_sqr(nxt)
+    assert nxt == _fq12(v["finally"])
+
+
+def test_cyclotomic_exp(golden):
+    # src/fields/mod.rs:229-344
+    v = golden["test_cyclotomic_exp"]
+    assert o.fq12_exp_by_neg_z(_fq12(v["orig"])) == _fq12(v["expected"])
+
+
+def test_prepared_g2(golden):
+    # src/groups/mod.rs:779-892: G2*Fr, to_affine and all 87 EllCoeffs
+    v = golden["test_prepared_g2"]
+    g2 = o.g_mul(o.FQ2_OPS, o.G2_ONE, int(v["g2_scalar"]))
+    qa = o.g_to_affine(o.FQ2_OPS, g2)
+    assert qa == (_fq2(v["q"]["x"]), _fq2(v["q"]["y"]))
+    q, coeffs = o.g2_precompute(qa)
+    assert len(coeffs) == 87
+    for got, exp in zip(coeffs, v["coeffs"]):
+        assert got == (_fq2(exp["ell_0"]), _fq2(exp["ell_vw"]), _fq2(exp["ell_vv"]))
+
+
+def test_miller_loop(golden):
+    # src/groups/mod.rs:642-691: the pre-final-exponentiation value
+    v = golden["test_miller_loop"]
+    g1 = o.g_mul(o.FQ_OPS, o.G1_ONE, int(v["g1_scalar"]))
+    g2 = o.g_mul(o.FQ2_OPS, o.G2_ONE, int(v["g2_scalar"]))
+    f = o.miller_loop(o.g2_precompute(o.g_to_affine(o.FQ2_OPS, g2)), o.g_to_affine(o.FQ_OPS, g1))
+    assert f == _fq12(v["expected"])
+
+
+def test_reduced_pairing(golden):
+    # src/groups/mod.rs:928-999
+    v = golden["test_reduced_pairing"]
+    g1 = o.g_mul(o.FQ_OPS, o.G1_ONE, int(v["g1_scalar"]))
+    g2 = o.g_mul(o.FQ2_OPS, o.G2_ONE, int(v["g2_scalar"]))
+    assert o.pairing(g1, g2) == _fq12(v["expected"])
+
+
+def test_batch_equals_product_and_edges():
+    """pairing_batch semantics (src/groups/mod.rs:904-926): skip infinity, empty -> one, product identity."""
+    p1 = o.g_mul(o.FQ_OPS, o.G1_ONE, 5)
+    p2 = o.g_mul(o.FQ_OPS, o.G1_ONE, 77)
+    q1 = o.g_mul(o.FQ2_OPS, o.G2_ONE, 9)
+    q2 = o.g_mul(o.FQ2_OPS, o.G2_ONE, 1234567)
+    assert o.pairing_batch([], []) == o.FQ12_ONE
+    assert o.pairing(o.g_zero(o.FQ_OPS), q1) == o.FQ12_ONE
+    assert o.pairing(p1, o.g_zero(o.FQ2_OPS)) == o.FQ12_ONE
+    b = o.pairing_batch([p1, o.g_zero(o.FQ_OPS), p2], [q1, q2, q2])
+    assert b == o.fq12_mul(o.pairing(p1, q1), o.pairing(p2, q2))
+    # bilinearity: e(5P, 9Q) == e(P,Q)^45
+    e = o.pairing(o.G1_ONE, o.G2_ONE)
+    assert o.pairing(p1, q1) == o.fq12_pow(e, 45)
+    # lib::miller_loop_batch error path
+    assert o.lib_miller_loop_batch([(o.g_zero(o.FQ2_OPS), p1)]) is None
+
+
+def test_g2_subgroup_and_group_law():
+    assert o.g2_in_subgroup(*o.G2_ONE[:2])
+    a = o.g_mul(o.FQ_OPS, o.G1_ONE, 12345)
+    b = o.g_mul(o.FQ_OPS, o.G1_ONE, 54321)
+    assert o.g_eq(o.FQ_OPS, o.g_add(o.FQ_OPS, a, b), o.g_mul(o.FQ_OPS, o.G1_ONE, 66666))
+    assert o.g_is_zero(o.FQ_OPS, o.g_add(o.FQ_OPS, o.g_mul(o.FQ_OPS, o.G1_ONE, o.R_ORDER - 1), o.G1_ONE))
