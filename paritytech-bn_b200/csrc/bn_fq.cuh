@@ -1,0 +1,258 @@
+// BN254 base field Fq on 8 x 32-bit limbs, Montgomery form (R = 2^256), always fully reduced.
+//
+// Replaces, on the device, the reference's U256 arithmetic (src/arith.rs:281-316 add/sub/neg,
+// :300-306 + :525-545 mul/mul_reduce) and the Fq newtype (src/fields/fp.rs:7-222).  The reference
+// uses 2 x u128 limbs and a radix-2^128 Montgomery step; both compute a*b*2^-256 mod q with a final
+// conditional subtraction, so the 32-byte little-endian memory image of every result is identical.
+//
+// Two back ends behind one interface:
+//   * device (__CUDA_ARCH__): the generated single-block PTX carry chains in fq_ptx.cuh
+//     (mad.lo.cc / madc.hi.cc -> IMAD.WIDE.U32[.X] on sm_100a);
+//   * host (BN_HOST_SIM, tests only): portable 64-bit C++ with the same results.  The shipped
+//     library never executes the host back end: every exported entry point launches kernels.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define BN_HD __host__ __device__ __forceinline__
+#define BN_HD_NOINLINE __host__ __device__ __noinline__
+#include "fq_ptx.cuh"
+#else
+#define BN_HD inline
+#define BN_HD_NOINLINE
+#endif
+
+namespace bn {
+
+struct Fq {
+    uint32_t v[8];
+};
+struct FqWide {  // 512-bit unreduced product (lazy reduction)
+    uint32_t v[16];
+};
+
+// q, little-endian 32-bit limbs (src/fields/fp.rs:197-202)
+#define BN_Q0 0xd87cfd47u
+#define BN_Q1 0x3c208c16u
+#define BN_Q2 0x6871ca8du
+#define BN_Q3 0x97816a91u
+#define BN_Q4 0x8181585du
+#define BN_Q5 0xb85045b6u
+#define BN_Q6 0xe131a029u
+#define BN_Q7 0x30644e72u
+#define BN_QINV32 0xe4866389u  // -q^-1 mod 2^32 (low word of src/fields/fp.rs:221)
+
+BN_HD uint32_t fq_modulus_limb(int i) {
+    switch (i) {
+        case 0: return BN_Q0; case 1: return BN_Q1; case 2: return BN_Q2; case 3: return BN_Q3;
+        case 4: return BN_Q4; case 5: return BN_Q5; case 6: return BN_Q6; default: return BN_Q7;
+    }
+}
+
+BN_HD bool fq_is_zero(const Fq& a) {
+    uint32_t x = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) x |= a.v[i];
+    return x == 0;
+}
+BN_HD bool fq_eq(const Fq& a, const Fq& b) {
+    uint32_t x = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) x |= a.v[i] ^ b.v[i];
+    return x == 0;
+}
+BN_HD void fq_set_zero(Fq& a) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) a.v[i] = 0;
+}
+
+#if !defined(__CUDA_ARCH__)
+// ---------------------------------------------------------------------------------------------
+// host back end (test-only simulation of the device arithmetic)
+// ---------------------------------------------------------------------------------------------
+namespace hostimpl {
+inline bool geq_q(const uint32_t* a) {
+    for (int i = 7; i >= 0; i--) {
+        uint32_t q = fq_modulus_limb(i);
+        if (a[i] != q) return a[i] > q;
+    }
+    return true;
+}
+inline void sub_q(uint32_t* a) {
+    int64_t br = 0;
+    for (int i = 0; i < 8; i++) {
+        int64_t d = (int64_t)a[i] - fq_modulus_limb(i) + br;
+        a[i] = (uint32_t)d;
+        br = d >> 32;
+    }
+}
+inline void mulwide(uint32_t* t, const uint32_t* a, const uint32_t* b) {
+    for (int i = 0; i < 16; i++) t[i] = 0;
+    for (int i = 0; i < 8; i++) {
+        uint64_t c = 0;
+        for (int j = 0; j < 8; j++) {
+            uint64_t s = (uint64_t)a[j] * b[i] + t[i + j] + c;
+            t[i + j] = (uint32_t)s;
+            c = s >> 32;
+        }
+        t[i + 8] = (uint32_t)c;
+    }
+}
+inline void redc(uint32_t* r, const uint32_t* tin) {
+    uint32_t t[17];
+    for (int i = 0; i < 16; i++) t[i] = tin[i];
+    t[16] = 0;
+    for (int i = 0; i < 8; i++) {
+        uint32_t k = t[i] * BN_QINV32;
+        uint64_t c = 0;
+        for (int j = 0; j < 8; j++) {
+            uint64_t s = (uint64_t)k * fq_modulus_limb(j) + t[i + j] + c;
+            t[i + j] = (uint32_t)s;
+            c = s >> 32;
+        }
+        for (int j = i + 8; c && j < 17; j++) {
+            uint64_t s = (uint64_t)t[j] + c;
+            t[j] = (uint32_t)s;
+            c = s >> 32;
+        }
+    }
+    for (int i = 0; i < 8; i++) r[i] = t[8 + i];
+    if (t[16] || geq_q(r)) sub_q(r);
+}
+}  // namespace hostimpl
+#endif
+
+BN_HD void fq_add(Fq& r, const Fq& a, const Fq& b) {  // src/arith.rs:281-287
+#if defined(__CUDA_ARCH__)
+    uint32_t t[8];
+    fq_add_ptx(t, a.v, b.v);
+#pragma unroll
+    for (int i = 0; i < 8; i++) r.v[i] = t[i];
+#else
+    uint32_t t[8];
+    uint64_t c = 0;
+    for (int i = 0; i < 8; i++) {
+        uint64_t s = (uint64_t)a.v[i] + b.v[i] + c;
+        t[i] = (uint32_t)s;
+        c = s >> 32;
+    }
+    if (hostimpl::geq_q(t)) hostimpl::sub_q(t);
+    for (int i = 0; i < 8; i++) r.v[i] = t[i];
+#endif
+}
+BN_HD void fq_sub(Fq& r, const Fq& a, const Fq& b) {  // src/arith.rs:290-296
+#if defined(__CUDA_ARCH__)
+    uint32_t t[8];
+    fq_sub_ptx(t, a.v, b.v);
+#pragma unroll
+    for (int i = 0; i < 8; i++) r.v[i] = t[i];
+#else
+    uint32_t t[8];
+    int64_t br = 0;
+    for (int i = 0; i < 8; i++) {
+        int64_t d = (int64_t)a.v[i] - b.v[i] + br;
+        t[i] = (uint32_t)d;
+        br = d >> 32;
+    }
+    if (br) {
+        uint64_t c = 0;
+        for (int i = 0; i < 8; i++) {
+            uint64_t s = (uint64_t)t[i] + fq_modulus_limb(i) + c;
+            t[i] = (uint32_t)s;
+            c = s >> 32;
+        }
+    }
+    for (int i = 0; i < 8; i++) r.v[i] = t[i];
+#endif
+}
+BN_HD void fq_neg(Fq& r, const Fq& a) {  // src/arith.rs:309-316 (0 -> 0)
+    Fq z;
+    fq_set_zero(z);
+    fq_sub(r, z, a);
+}
+BN_HD void fq_dbl(Fq& r, const Fq& a) { fq_add(r, a, a); }
+
+BN_HD void fq_mul(Fq& r, const Fq& a, const Fq& b) {  // src/arith.rs:300-306, :525-545
+#if defined(__CUDA_ARCH__)
+    uint32_t t[8];
+    fq_mul_ptx(t, a.v, b.v);
+#pragma unroll
+    for (int i = 0; i < 8; i++) r.v[i] = t[i];
+#else
+    uint32_t w[16], t[8];
+    hostimpl::mulwide(w, a.v, b.v);
+    hostimpl::redc(t, w);
+    for (int i = 0; i < 8; i++) r.v[i] = t[i];
+#endif
+}
+BN_HD void fq_sqr(Fq& r, const Fq& a) { fq_mul(r, a, a); }
+
+// ---- lazy-reduction helpers: 512-bit products, reduced once per output coefficient ----------
+BN_HD void fq_mulwide(FqWide& t, const Fq& a, const Fq& b) {
+#if defined(__CUDA_ARCH__)
+    fq_mulwide_ptx(t.v, a.v, b.v);
+#else
+    hostimpl::mulwide(t.v, a.v, b.v);
+#endif
+}
+BN_HD void fq_redc(Fq& r, const FqWide& t) {  // t < q*2^256
+#if defined(__CUDA_ARCH__)
+    uint32_t o[8];
+    fq_redc_ptx(o, t.v);
+#pragma unroll
+    for (int i = 0; i < 8; i++) r.v[i] = o[i];
+#else
+    hostimpl::redc(r.v, t.v);
+#endif
+}
+BN_HD void wide_add(FqWide& a, const FqWide& b) {  // a += b (caller guarantees a+b < 2^512)
+#if defined(__CUDA_ARCH__)
+    wide_add_ptx(a.v, b.v);
+#else
+    uint64_t c = 0;
+    for (int i = 0; i < 16; i++) {
+        uint64_t s = (uint64_t)a.v[i] + b.v[i] + c;
+        a.v[i] = (uint32_t)s;
+        c = s >> 32;
+    }
+#endif
+}
+BN_HD void wide_sub(FqWide& a, const FqWide& b) {  // a -= b; on borrow add q*2^256 (stays in [0, qR))
+#if defined(__CUDA_ARCH__)
+    wide_sub_ptx(a.v, b.v);
+#else
+    int64_t br = 0;
+    for (int i = 0; i < 16; i++) {
+        int64_t d = (int64_t)a.v[i] - b.v[i] + br;
+        a.v[i] = (uint32_t)d;
+        br = d >> 32;
+    }
+    if (br) {
+        uint64_t c = 0;
+        for (int i = 0; i < 8; i++) {
+            uint64_t s = (uint64_t)a.v[8 + i] + fq_modulus_limb(i) + c;
+            a.v[8 + i] = (uint32_t)s;
+            c = s >> 32;
+        }
+    }
+#endif
+}
+// plain 256-bit add without reduction (for Karatsuba sums a0+a1 < 2q < 2^256)
+BN_HD void fq_add_noreduce(Fq& r, const Fq& a, const Fq& b) {
+#if defined(__CUDA_ARCH__)
+    asm("add.cc.u32 %0, %8, %16;\n\taddc.cc.u32 %1, %9, %17;\n\taddc.cc.u32 %2, %10, %18;\n\taddc.cc.u32 %3, %11, %19;\n\t"
+        "addc.cc.u32 %4, %12, %20;\n\taddc.cc.u32 %5, %13, %21;\n\taddc.cc.u32 %6, %14, %22;\n\taddc.u32 %7, %15, %23;"
+        : "=&r"(r.v[0]), "=&r"(r.v[1]), "=&r"(r.v[2]), "=&r"(r.v[3]), "=&r"(r.v[4]), "=&r"(r.v[5]), "=&r"(r.v[6]), "=&r"(r.v[7])
+        : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]),
+          "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+#else
+    uint64_t c = 0;
+    for (int i = 0; i < 8; i++) {
+        uint64_t s = (uint64_t)a.v[i] + b.v[i] + c;
+        r.v[i] = (uint32_t)s;
+        c = s >> 32;
+    }
+#endif
+}
+
+}  // namespace bn
