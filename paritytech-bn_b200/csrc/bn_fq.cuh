@@ -24,10 +24,10 @@
 
 namespace bn {
 
-struct Fq {
+struct alignas(16) Fq {
     uint32_t v[8];
 };
-struct FqWide {  // 512-bit unreduced product (lazy reduction)
+struct alignas(16) FqWide {  // 512-bit unreduced product (lazy reduction)
     uint32_t v[16];
 };
 

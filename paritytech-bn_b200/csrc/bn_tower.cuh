@@ -1,0 +1,380 @@
+// Field tower Fq2 -> Fq6 -> Fq12 for BN254, "lean" evaluation of the reference's formulas:
+// same field elements (hence the same fully-reduced Montgomery bytes) as src/fields/{fq2,fq6,fq12}.rs,
+// but multiplication by -1, by xi = 9+u and conjugation are done with additions, Fq2 products use
+// lazy reduction (3 wide products, 2 Montgomery reductions), and inversions use Fermat (a^(q-2)) --
+// SURVEY.md 8a rows A3, A5-A8, A14-A16 explain why any exact evaluation is bit-identical.
+//
+// All functions are alias-safe (outputs may alias inputs).  Big ones are __noinline__ on the device
+// so the kernels stay a few hundred KB of SASS and Fq12 state lives in per-thread local memory
+// while each Fq2-level body is register-blocked.
+#pragma once
+#include "bn_consts.cuh"
+#include "bn_fq.cuh"
+
+namespace bn {
+
+struct Fq2 { Fq c0, c1; };            // src/fields/fq2.rs:36-41 (repr(C))
+struct Fq6 { Fq2 c0, c1, c2; };       // src/fields/fq6.rs:92-98
+struct Fq12 { Fq6 c0, c1; };          // src/fields/fq12.rs:50-55
+
+BN_HD Fq fq_one() { Fq r = BN_C_ONE; return r; }
+BN_HD Fq fq_zero() { Fq r; fq_set_zero(r); return r; }
+
+// ---------------------------------------------------------------------------------------------
+// Fq helpers: Fermat inversion (replaces the divergent binary EEA of src/arith.rs:324-370)
+// ---------------------------------------------------------------------------------------------
+BN_HD_NOINLINE void fq_mul_ni(Fq& r, const Fq& a, const Fq& b) { fq_mul(r, a, b); }
+
+// r = a^(q-2); returns false (and r = 0) for a == 0, like Fq::inverse -> None (src/fields/fp.rs:108-117)
+BN_HD_NOINLINE bool fq_inv(Fq& r, const Fq& a) {
+    if (fq_is_zero(a)) { fq_set_zero(r); return false; }
+    const uint32_t e[8] = BN_Q_MINUS_2_LIMBS;
+    Fq acc = a;  // top bit (bit 253) is set
+    for (int i = 252; i >= 0; i--) {
+        fq_mul_ni(acc, acc, acc);
+        if ((e[i >> 5] >> (i & 31)) & 1) fq_mul_ni(acc, acc, a);
+    }
+    r = acc;
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fq2 = Fq[u]/(u^2+1)
+// ---------------------------------------------------------------------------------------------
+BN_HD Fq2 fq2_zero() { Fq2 r; fq_set_zero(r.c0); fq_set_zero(r.c1); return r; }
+BN_HD Fq2 fq2_one() { Fq2 r; r.c0 = fq_one(); fq_set_zero(r.c1); return r; }
+BN_HD bool fq2_is_zero(const Fq2& a) { return fq_is_zero(a.c0) && fq_is_zero(a.c1); }
+BN_HD bool fq2_eq(const Fq2& a, const Fq2& b) { return fq_eq(a.c0, b.c0) && fq_eq(a.c1, b.c1); }
+BN_HD void fq2_add(Fq2& r, const Fq2& a, const Fq2& b) { fq_add(r.c0, a.c0, b.c0); fq_add(r.c1, a.c1, b.c1); }
+BN_HD void fq2_sub(Fq2& r, const Fq2& a, const Fq2& b) { fq_sub(r.c0, a.c0, b.c0); fq_sub(r.c1, a.c1, b.c1); }
+BN_HD void fq2_neg(Fq2& r, const Fq2& a) { fq_neg(r.c0, a.c0); fq_neg(r.c1, a.c1); }
+BN_HD void fq2_dbl(Fq2& r, const Fq2& a) { fq_dbl(r.c0, a.c0); fq_dbl(r.c1, a.c1); }
+BN_HD void fq2_conj(Fq2& r, const Fq2& a) { r.c0 = a.c0; fq_neg(r.c1, a.c1); }   // frobenius_map(odd), fq2.rs:59-68
+
+// Karatsuba with lazy reduction; value of src/fields/fq2.rs:133-149
+BN_HD void fq2_mul_inl(Fq2& r, const Fq2& a, const Fq2& b) {
+    FqWide t0, t1, s;
+    Fq sa, sb;
+    fq_mulwide(t0, a.c0, b.c0);
+    fq_mulwide(t1, a.c1, b.c1);
+    fq_add_noreduce(sa, a.c0, a.c1);
+    fq_add_noreduce(sb, b.c0, b.c1);
+    fq_mulwide(s, sa, sb);          // < 4q^2 < q*2^256
+    wide_sub(s, t0);                // >= 0: a0*b1 + a1*b0 + t1
+    wide_sub(s, t1);                // a0*b1 + a1*b0 < 2q^2
+    wide_sub(t0, t1);               // a0*b0 - a1*b1 (+ q*2^256 if negative)
+    fq_redc(r.c0, t0);
+    fq_redc(r.c1, s);
+}
+BN_HD_NOINLINE void fq2_mul(Fq2& r, const Fq2& a, const Fq2& b) { fq2_mul_inl(r, a, b); }
+
+// complex squaring; value of src/fields/fq2.rs:105-117
+BN_HD void fq2_sqr_inl(Fq2& r, const Fq2& a) {
+    Fq s, d, m;
+    fq_add_noreduce(s, a.c0, a.c1);   // < 2q, fine as a Montgomery multiplicand
+    fq_sub(d, a.c0, a.c1);
+    fq_mul(m, a.c0, a.c1);
+    fq_mul(r.c0, s, d);
+    fq_dbl(r.c1, m);
+}
+BN_HD_NOINLINE void fq2_sqr(Fq2& r, const Fq2& a) { fq2_sqr_inl(r, a); }
+
+BN_HD_NOINLINE void fq2_scale(Fq2& r, const Fq2& a, const Fq& k) {   // src/fields/fq2.rs:48-53
+    fq_mul(r.c0, a.c0, k);
+    fq_mul(r.c1, a.c1, k);
+}
+// a * (9 + u) = (9 a0 - a1) + (9 a1 + a0) u; value of src/fields/fq2.rs:55-57
+BN_HD void fq2_mul_by_xi(Fq2& r, const Fq2& a) {
+    Fq t0, t1, n0, n1;
+    fq_dbl(t0, a.c0); fq_dbl(t0, t0); fq_dbl(t0, t0); fq_add(t0, t0, a.c0);   // 9 a0
+    fq_dbl(t1, a.c1); fq_dbl(t1, t1); fq_dbl(t1, t1); fq_add(t1, t1, a.c1);   // 9 a1
+    fq_sub(n0, t0, a.c1);
+    fq_add(n1, t1, a.c0);
+    r.c0 = n0;
+    r.c1 = n1;
+}
+BN_HD_NOINLINE bool fq2_inv(Fq2& r, const Fq2& a) {   // src/fields/fq2.rs:119-130
+    Fq n, t, t2;
+    fq_sqr(n, a.c0);
+    fq_sqr(t, a.c1);
+    fq_add(n, n, t);
+    if (!fq_inv(t, n)) { r = fq2_zero(); return false; }
+    fq_mul(r.c0, a.c0, t);
+    fq_mul(t2, a.c1, t);
+    fq_neg(r.c1, t2);
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fq6 = Fq2[v]/(v^3 - xi)
+// ---------------------------------------------------------------------------------------------
+BN_HD Fq6 fq6_zero() { Fq6 r; r.c0 = fq2_zero(); r.c1 = fq2_zero(); r.c2 = fq2_zero(); return r; }
+BN_HD Fq6 fq6_one() { Fq6 r = fq6_zero(); r.c0.c0 = fq_one(); return r; }
+BN_HD void fq6_add(Fq6& r, const Fq6& a, const Fq6& b) { fq2_add(r.c0, a.c0, b.c0); fq2_add(r.c1, a.c1, b.c1); fq2_add(r.c2, a.c2, b.c2); }
+BN_HD void fq6_sub(Fq6& r, const Fq6& a, const Fq6& b) { fq2_sub(r.c0, a.c0, b.c0); fq2_sub(r.c1, a.c1, b.c1); fq2_sub(r.c2, a.c2, b.c2); }
+BN_HD void fq6_neg(Fq6& r, const Fq6& a) { fq2_neg(r.c0, a.c0); fq2_neg(r.c1, a.c1); fq2_neg(r.c2, a.c2); }
+BN_HD void fq6_dbl(Fq6& r, const Fq6& a) { fq2_dbl(r.c0, a.c0); fq2_dbl(r.c1, a.c1); fq2_dbl(r.c2, a.c2); }
+BN_HD bool fq6_is_zero(const Fq6& a) { return fq2_is_zero(a.c0) && fq2_is_zero(a.c1) && fq2_is_zero(a.c2); }
+BN_HD void fq6_mul_by_v(Fq6& r, const Fq6& a) {   // mul_by_nonresidue, src/fields/fq6.rs:109-115
+    Fq2 t;
+    fq2_mul_by_xi(t, a.c2);
+    r.c2 = a.c1;
+    r.c1 = a.c0;
+    r.c0 = t;
+}
+BN_HD_NOINLINE void fq6_mul(Fq6& r, const Fq6& a, const Fq6& b) {   // value of src/fields/fq6.rs:194-208
+    Fq2 aa, bb, cc, t, u, s;
+    fq2_mul(aa, a.c0, b.c0);
+    fq2_mul(bb, a.c1, b.c1);
+    fq2_mul(cc, a.c2, b.c2);
+    Fq2 n0, n1, n2;
+    fq2_add(t, a.c1, a.c2); fq2_add(u, b.c1, b.c2); fq2_mul(s, t, u);
+    fq2_sub(s, s, bb); fq2_sub(s, s, cc); fq2_mul_by_xi(s, s); fq2_add(n0, s, aa);
+    fq2_add(t, a.c0, a.c1); fq2_add(u, b.c0, b.c1); fq2_mul(s, t, u);
+    fq2_sub(s, s, aa); fq2_sub(s, s, bb); fq2_mul_by_xi(t, cc); fq2_add(n1, s, t);
+    fq2_add(t, a.c0, a.c2); fq2_add(u, b.c0, b.c2); fq2_mul(s, t, u);
+    fq2_sub(s, s, aa); fq2_add(s, s, bb); fq2_sub(n2, s, cc);
+    r.c0 = n0; r.c1 = n1; r.c2 = n2;
+}
+BN_HD_NOINLINE void fq6_sqr(Fq6& r, const Fq6& a) {   // value of src/fields/fq6.rs:163-177
+    Fq2 s0, s1, s2, s3, s4, t;
+    fq2_sqr(s0, a.c0);
+    fq2_mul(s1, a.c0, a.c1); fq2_dbl(s1, s1);
+    fq2_sub(t, a.c0, a.c1); fq2_add(t, t, a.c2); fq2_sqr(s2, t);
+    fq2_mul(s3, a.c1, a.c2); fq2_dbl(s3, s3);
+    fq2_sqr(s4, a.c2);
+    Fq2 n0, n1, n2;
+    fq2_mul_by_xi(t, s3); fq2_add(n0, s0, t);
+    fq2_mul_by_xi(t, s4); fq2_add(n1, s1, t);
+    fq2_add(n2, s1, s2); fq2_add(n2, n2, s3); fq2_sub(n2, n2, s0); fq2_sub(n2, n2, s4);
+    r.c0 = n0; r.c1 = n1; r.c2 = n2;
+}
+BN_HD_NOINLINE void fq6_scale(Fq6& r, const Fq6& a, const Fq2& k) {   // src/fields/fq6.rs:117-123
+    fq2_mul(r.c0, a.c0, k); fq2_mul(r.c1, a.c1, k); fq2_mul(r.c2, a.c2, k);
+}
+BN_HD_NOINLINE bool fq6_inv(Fq6& r, const Fq6& a) {   // src/fields/fq6.rs:179-191
+    Fq2 c0, c1, c2, t, u;
+    fq2_mul_by_xi(t, a.c2); fq2_mul(t, a.c1, t); fq2_sqr(c0, a.c0); fq2_sub(c0, c0, t);
+    fq2_sqr(t, a.c2); fq2_mul_by_xi(t, t); fq2_mul(u, a.c0, a.c1); fq2_sub(c1, t, u);
+    fq2_sqr(t, a.c1); fq2_mul(u, a.c0, a.c2); fq2_sub(c2, t, u);
+    fq2_mul(t, a.c2, c1); fq2_mul(u, a.c1, c2); fq2_add(t, t, u); fq2_mul_by_xi(t, t);
+    fq2_mul(u, a.c0, c0); fq2_add(t, t, u);
+    if (!fq2_inv(u, t)) { r = fq6_zero(); return false; }
+    fq2_mul(r.c0, u, c0); fq2_mul(r.c1, u, c1); fq2_mul(r.c2, u, c2);
+    return true;
+}
+// Frobenius: conjugate each Fq2 coefficient for odd powers, multiply by xi^(i(q^k-1)/3); fq6.rs:125-131
+BN_HD void fq6_frobenius(Fq6& r, const Fq6& a, int power) {
+    const Fq2 c1tab[3] = {BN_C_FROB6_C1_1, BN_C_FROB6_C1_2, BN_C_FROB6_C1_3};
+    const Fq2 c2tab[3] = {BN_C_FROB6_C2_1, BN_C_FROB6_C2_2, BN_C_FROB6_C2_3};
+    Fq2 x0 = a.c0, x1 = a.c1, x2 = a.c2;
+    if (power & 1) { fq2_conj(x0, x0); fq2_conj(x1, x1); fq2_conj(x2, x2); }
+    r.c0 = x0;
+    fq2_mul(r.c1, x1, c1tab[power - 1]);
+    fq2_mul(r.c2, x2, c2tab[power - 1]);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Fq12 = Fq6[w]/(w^2 - v)
+// ---------------------------------------------------------------------------------------------
+BN_HD Fq12 fq12_one() { Fq12 r; r.c0 = fq6_one(); r.c1 = fq6_zero(); return r; }
+BN_HD Fq12 fq12_zero() { Fq12 r; r.c0 = fq6_zero(); r.c1 = fq6_zero(); return r; }
+BN_HD bool fq12_eq(const Fq12& a, const Fq12& b) {   // derived PartialEq on Gt, src/lib.rs:584
+    const uint32_t* x = (const uint32_t*)&a;
+    const uint32_t* y = (const uint32_t*)&b;
+    uint32_t d = 0;
+    for (int i = 0; i < 96; i++) d |= x[i] ^ y[i];
+    return d == 0;
+}
+BN_HD_NOINLINE void fq12_mul(Fq12& r, const Fq12& a, const Fq12& b) {   // value of src/fields/fq12.rs:316-328
+    Fq6 aa, bb, s, t, u;
+    fq6_mul(aa, a.c0, b.c0);
+    fq6_mul(bb, a.c1, b.c1);
+    fq6_add(t, a.c0, a.c1);
+    fq6_add(u, b.c0, b.c1);
+    fq6_mul(s, t, u);
+    fq6_sub(s, s, aa);
+    fq6_sub(r.c1, s, bb);
+    fq6_mul_by_v(t, bb);
+    fq6_add(r.c0, t, aa);
+}
+BN_HD_NOINLINE void fq12_sqr(Fq12& r, const Fq12& a) {   // value of src/fields/fq12.rs:295-303
+    Fq6 ab, t, u, s;
+    fq6_mul(ab, a.c0, a.c1);
+    fq6_mul_by_v(t, a.c1);
+    fq6_add(t, t, a.c0);
+    fq6_add(u, a.c0, a.c1);
+    fq6_mul(s, t, u);
+    fq6_sub(s, s, ab);
+    fq6_mul_by_v(t, ab);
+    fq6_sub(r.c0, s, t);
+    fq6_dbl(r.c1, ab);
+}
+BN_HD void fq12_conj(Fq12& r, const Fq12& a) { r.c0 = a.c0; fq6_neg(r.c1, a.c1); }   // unitary_inverse, fq12.rs:126-128
+BN_HD_NOINLINE bool fq12_inv(Fq12& r, const Fq12& a) {   // src/fields/fq12.rs:305-313
+    Fq6 t, u;
+    fq6_sqr(t, a.c0);
+    fq6_sqr(u, a.c1);
+    fq6_mul_by_v(u, u);
+    fq6_sub(t, t, u);
+    if (!fq6_inv(u, t)) { r = fq12_zero(); return false; }
+    fq6_mul(r.c0, a.c0, u);
+    fq6_mul(t, a.c1, u);
+    fq6_neg(r.c1, t);
+    return true;
+}
+BN_HD_NOINLINE void fq12_frobenius(Fq12& r, const Fq12& a, int power) {   // src/fields/fq12.rs:112-119
+    const Fq2 ctab[3] = {BN_C_FROB12_C1_1, BN_C_FROB12_C1_2, BN_C_FROB12_C1_3};
+    Fq6 t;
+    fq6_frobenius(r.c0, a.c0, power);
+    fq6_frobenius(t, a.c1, power);
+    fq6_scale(r.c1, t, ctab[power - 1]);
+}
+
+// f * (ell_0 + ell_vv v + ell_vw v w): sparse multiply; value of src/fields/fq12.rs:130-196.
+// x0 = ell_0, x2 = ell_vv, x4 = ell_vw (already scaled by P.x / P.y by the caller).
+BN_HD_NOINLINE void fq12_mul_by_024(Fq12& f, const Fq2& x0, const Fq2& x4, const Fq2& x2) {
+    Fq2 z0 = f.c0.c0, z1 = f.c0.c1, z2 = f.c0.c2, z3 = f.c1.c0, z4 = f.c1.c1, z5 = f.c1.c2;
+    Fq2 d0, d2, d4, s0, s1, t0, t1, t2, t3, t4;
+    fq2_mul(d0, z0, x0);
+    fq2_mul(d2, z2, x2);
+    fq2_mul(d4, z4, x4);
+    fq2_add(t2, z0, z4);
+    fq2_add(t1, z0, z2);
+    fq2_add(s0, z1, z3); fq2_add(s0, s0, z5);
+
+    fq2_mul(s1, z1, x2);
+    fq2_add(t3, s1, d4);
+    fq2_mul_by_xi(t4, t3); fq2_add(f.c0.c0, t4, d0);          // z0'
+
+    fq2_mul(t3, z5, x4);
+    fq2_add(s1, s1, t3);
+    fq2_add(t3, t3, d2);
+    fq2_mul_by_xi(t4, t3);
+    fq2_mul(t3, z1, x0);
+    fq2_add(s1, s1, t3);
+    fq2_add(f.c0.c1, t4, t3);                                  // z1'
+
+    fq2_add(t0, x0, x2);
+    fq2_mul(t3, t1, t0); fq2_sub(t3, t3, d0); fq2_sub(t3, t3, d2);
+    fq2_mul(t4, z3, x4);
+    fq2_add(s1, s1, t4);
+    fq2_add(t0, z2, z4);
+    fq2_add(f.c0.c2, t3, t4);                                  // z2'
+
+    fq2_add(t1, x2, x4);
+    fq2_mul(t3, t0, t1); fq2_sub(t3, t3, d2); fq2_sub(t3, t3, d4);
+    fq2_mul_by_xi(t4, t3);
+    fq2_mul(t3, z3, x0);
+    fq2_add(s1, s1, t3);
+    fq2_add(f.c1.c0, t4, t3);                                  // z3'
+
+    fq2_mul(t3, z5, x2);
+    fq2_add(s1, s1, t3);
+    fq2_mul_by_xi(t4, t3);
+    fq2_add(t0, x0, x4);
+    fq2_mul(t3, t2, t0); fq2_sub(t3, t3, d0); fq2_sub(t3, t3, d4);
+    fq2_add(f.c1.c1, t4, t3);                                  // z4'
+
+    fq2_add(t0, x0, x2); fq2_add(t0, t0, x4);
+    fq2_mul(t3, s0, t0);
+    fq2_sub(f.c1.c2, t3, s1);                                  // z5'
+}
+
+// Granger-Scott squaring in the cyclotomic subgroup; value of src/fields/fq12.rs:198-247.
+// One "Fq4 squaring" (a, b) -> (a^2 + xi b^2, 2ab) per coefficient pair.
+BN_HD void fq4_sqr(Fq2& r0, Fq2& r1, const Fq2& a, const Fq2& b) {
+    Fq2 tmp, s, t, u;
+    fq2_mul(tmp, a, b);
+    fq2_add(s, a, b);
+    fq2_mul_by_xi(t, b); fq2_add(t, t, a);
+    fq2_mul(s, s, t);
+    fq2_sub(s, s, tmp);
+    fq2_mul_by_xi(u, tmp);
+    fq2_sub(r0, s, u);
+    fq2_dbl(r1, tmp);
+}
+BN_HD_NOINLINE void fq12_cyclotomic_sqr(Fq12& r, const Fq12& a) {
+    Fq2 z0 = a.c0.c0, z4 = a.c0.c1, z3 = a.c0.c2, z2 = a.c1.c0, z1 = a.c1.c1, z5 = a.c1.c2;
+    Fq2 t0, t1, t2, t3, t4, t5, tmp;
+    fq4_sqr(t0, t1, z0, z1);
+    fq4_sqr(t2, t3, z2, z3);
+    fq4_sqr(t4, t5, z4, z5);
+    fq2_sub(z0, t0, z0); fq2_dbl(z0, z0); fq2_add(z0, z0, t0);
+    fq2_add(z1, t1, z1); fq2_dbl(z1, z1); fq2_add(z1, z1, t1);
+    fq2_mul_by_xi(tmp, t5);
+    fq2_add(z2, tmp, z2); fq2_dbl(z2, z2); fq2_add(z2, z2, tmp);
+    fq2_sub(z3, t4, z3); fq2_dbl(z3, z3); fq2_add(z3, z3, t4);
+    fq2_sub(z4, t2, z4); fq2_dbl(z4, z4); fq2_add(z4, z4, t2);
+    fq2_add(z5, t3, z5); fq2_dbl(z5, z5); fq2_add(z5, z5, t3);
+    r.c0.c0 = z0; r.c0.c1 = z4; r.c0.c2 = z3;
+    r.c1.c0 = z2; r.c1.c1 = z1; r.c1.c2 = z5;
+}
+// conj(a^u), u = 4965661367192848881 (63 bits); value of src/fields/fq12.rs:121-124 + :249-266.
+// (The reference's multiply-by-one on the first set bit is skipped: same value.)
+BN_HD_NOINLINE void fq12_exp_by_neg_z(Fq12& r, const Fq12& a) {
+    const uint64_t u = ((uint64_t)BN_U_HI << 32) | BN_U_LO;
+    Fq12 acc = a;  // bit 62
+    for (int i = 61; i >= 0; i--) {
+        fq12_cyclotomic_sqr(acc, acc);
+        if ((u >> i) & 1) fq12_mul(acc, acc, a);
+    }
+    fq12_conj(r, acc);
+}
+// easy part f^((q^6-1)(q^2+1)); false iff f == 0.  src/fields/fq12.rs:62-73
+BN_HD_NOINLINE bool fq12_final_exp_first_chunk(Fq12& r, const Fq12& f) {
+    Fq12 b, a, c;
+    if (!fq12_inv(b, f)) { r = fq12_zero(); return false; }
+    fq12_conj(a, f);
+    fq12_mul(c, a, b);
+    fq12_frobenius(a, c, 2);
+    fq12_mul(r, a, c);
+    return true;
+}
+// hard part, the reference's addition chain; src/fields/fq12.rs:75-105 (same step names)
+BN_HD_NOINLINE void fq12_final_exp_last_chunk(Fq12& out, const Fq12& x) {
+    Fq12 a, b, c, d, e, f, g, k, l, t;
+    fq12_exp_by_neg_z(a, x);
+    fq12_cyclotomic_sqr(b, a);
+    fq12_cyclotomic_sqr(c, b);
+    fq12_mul(d, c, b);
+    fq12_exp_by_neg_z(e, d);
+    fq12_cyclotomic_sqr(f, e);
+    fq12_exp_by_neg_z(g, f);
+    fq12_conj(d, d);              // h
+    fq12_conj(g, g);              // i
+    fq12_mul(t, g, e);            // j
+    fq12_mul(k, t, d);            // k
+    fq12_mul(l, k, b);            // l
+    fq12_mul(t, k, e);            // m
+    fq12_mul(t, x, t);            // n
+    fq12_frobenius(a, l, 1);      // o
+    fq12_mul(t, a, t);            // p
+    fq12_frobenius(a, k, 2);      // q
+    fq12_mul(t, a, t);            // r
+    fq12_conj(a, x);              // s
+    fq12_mul(a, a, l);            // t
+    fq12_frobenius(b, a, 3);      // u
+    fq12_mul(out, b, t);          // v
+}
+BN_HD bool fq12_final_exponentiation(Fq12& r, const Fq12& f) {   // src/fields/fq12.rs:107-110
+    Fq12 t;
+    if (!fq12_final_exp_first_chunk(t, f)) { r = fq12_zero(); return false; }
+    fq12_final_exp_last_chunk(r, t);
+    return true;
+}
+// FieldElement::pow over the 256 bits of a canonical scalar (Gt::pow, src/lib.rs:592 -> fields/mod.rs:35-46).
+// Leading zero bits only square 1, so skipping them gives the same value.
+BN_HD_NOINLINE void fq12_pow(Fq12& r, const Fq12& a, const uint32_t (&k)[8]) {
+    Fq12 acc = fq12_one();
+    bool started = false;
+    for (int i = 255; i >= 0; i--) {
+        if (started) fq12_sqr(acc, acc);
+        if ((k[i >> 5] >> (i & 31)) & 1) {
+            if (started) fq12_mul(acc, acc, a); else { acc = a; started = true; }
+        }
+    }
+    r = acc;
+}
+
+}  // namespace bn

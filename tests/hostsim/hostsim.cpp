@@ -1,0 +1,93 @@
+// TEST-ONLY host build of the device headers (bn_fq/bn_tower/bn_curve .cuh) with the portable
+// arithmetic back end.  Lets the CPU test-suite check every formula, constant and control path
+// of the CUDA code against the oracle without a GPU.  Never linked into the shipped library.
+#include <stddef.h>
+#include <string.h>
+#define BN_HOST_SIM 1
+#include "../../paritytech-bn_b200/csrc/bn_curve.cuh"
+using namespace bn;
+
+template <class T> static T ld(const void* p, size_t i) { T v; memcpy(&v, (const char*)p + i * sizeof(T), sizeof(T)); return v; }
+template <class T> static void st(void* p, size_t i, const T& v) { memcpy((char*)p + i * sizeof(T), &v, sizeof(T)); }
+
+#define BIN(name, T, fn) extern "C" void hs_##name(const void* a, const void* b, void* o, size_t n) { \
+    for (size_t i = 0; i < n; i++) { T x = ld<T>(a, i), y = ld<T>(b, i), r; fn(r, x, y); st(o, i, r); } }
+#define UN(name, T, fn) extern "C" void hs_##name(const void* a, void* o, size_t n) { \
+    for (size_t i = 0; i < n; i++) { T x = ld<T>(a, i), r; fn(r, x); st(o, i, r); } }
+// in-place variants exercise the alias-safety the kernels rely on
+#define BIN_ALIAS(name, T, fn) extern "C" void hs_##name##_alias(const void* a, const void* b, void* o, size_t n) { \
+    for (size_t i = 0; i < n; i++) { T x = ld<T>(a, i), y = ld<T>(b, i); fn(x, x, y); st(o, i, x); } }
+
+BIN(fq_mul, Fq, fq_mul) BIN(fq_add, Fq, fq_add) BIN(fq_sub, Fq, fq_sub)
+BIN(fq2_mul, Fq2, fq2_mul) UN(fq2_sqr, Fq2, fq2_sqr) UN(fq2_mul_by_xi, Fq2, fq2_mul_by_xi) UN(fq2_half, Fq2, fq2_half)
+BIN(fq6_mul, Fq6, fq6_mul) UN(fq6_sqr, Fq6, fq6_sqr)
+BIN(fq12_mul, Fq12, fq12_mul) UN(fq12_sqr, Fq12, fq12_sqr)
+BIN_ALIAS(fq2_mul, Fq2, fq2_mul) BIN_ALIAS(fq6_mul, Fq6, fq6_mul) BIN_ALIAS(fq12_mul, Fq12, fq12_mul)
+UN(fq12_cyclotomic_sqr, Fq12, fq12_cyclotomic_sqr) UN(fq12_exp_by_neg_z, Fq12, fq12_exp_by_neg_z)
+UN(fq12_final_exp_last_chunk, Fq12, fq12_final_exp_last_chunk)
+BIN(g1_add, G1, jac_add) BIN(g2_add, G2, jac_add) UN(g1_double, G1, jac_double) UN(g2_double, G2, jac_double)
+UN(g1_normalize, G1, jac_normalize) UN(g2_normalize, G2, jac_normalize)
+
+extern "C" void hs_fq_inv(const void* a, void* o, unsigned char* some, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r; some[i] = fq_inv(r, x); st(o, i, r); }
+}
+extern "C" void hs_fq12_inv(const void* a, void* o, unsigned char* some, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq12 x = ld<Fq12>(a, i), r; some[i] = fq12_inv(r, x); st(o, i, r); }
+}
+extern "C" void hs_final_exp(const void* a, void* o, unsigned char* some, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq12 x = ld<Fq12>(a, i), r; some[i] = fq12_final_exponentiation(r, x); st(o, i, r); }
+}
+extern "C" void hs_fq12_frobenius(const void* a, int power, void* o, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq12 x = ld<Fq12>(a, i), r; fq12_frobenius(r, x, power); st(o, i, r); }
+}
+extern "C" void hs_fq12_mul_by_024(const void* f, const void* ell, void* o, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq12 x = ld<Fq12>(f, i); EllCoeffs c = ld<EllCoeffs>(ell, i); fq12_mul_by_024(x, c.ell_0, c.ell_vw, c.ell_vv); st(o, i, x); }
+}
+extern "C" void hs_gt_pow(const void* a, const void* fr, void* o, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        Fq12 x = ld<Fq12>(a, i), r; Fq m = ld<Fq>(fr, i); uint32_t k[8]; fr_to_canonical(k, m.v); fq12_pow(r, x, k); st(o, i, r);
+    }
+}
+extern "C" void hs_g1_mul(const void* p, const void* fr, void* o, size_t n) {
+    for (size_t i = 0; i < n; i++) { G1 x = ld<G1>(p, i), r; Fq m = ld<Fq>(fr, i); uint32_t k[8]; fr_to_canonical(k, m.v); jac_mul(r, x, k); st(o, i, r); }
+}
+extern "C" void hs_g2_mul(const void* p, const void* fr, void* o, size_t n) {
+    for (size_t i = 0; i < n; i++) { G2 x = ld<G2>(p, i), r; Fq m = ld<Fq>(fr, i); uint32_t k[8]; fr_to_canonical(k, m.v); jac_mul(r, x, k); st(o, i, r); }
+}
+extern "C" void hs_fr_to_canonical(const void* fr, void* o, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq m = ld<Fq>(fr, i), r; fr_to_canonical(r.v, m.v); st(o, i, r); }
+}
+// G2Precomp image: q (128 B) + 87 x EllCoeffs; returns 0 at infinity
+extern "C" int hs_g2_precompute(const void* q, void* o) {
+    G2 x = ld<G2>(q, 0); AffG2 qa;
+    if (!jac_to_affine(qa, x)) return 0;
+    EllCoeffs tab[BN_N_COEFFS];
+    StoreSink s; s.out = tab; s.n = 0;
+    g2_walk_lines(qa, s);
+    if (s.n != BN_N_COEFFS) return -1;
+    memcpy(o, &qa, sizeof qa);
+    memcpy((char*)o + sizeof qa, tab, sizeof tab);
+    return 1;
+}
+extern "C" void hs_miller_loop(const void* q, const void* p, void* o, unsigned char* ok, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        G1 pp = ld<G1>(p, i); G2 qq = ld<G2>(q, i); AffG1 pa; AffG2 qa; Fq12 f = fq12_one();
+        bool good = jac_to_affine(pa, pp) & jac_to_affine(qa, qq);
+        if (good) miller_loop_fused(f, pa, qa);
+        ok[i] = good; st(o, i, f);
+    }
+}
+extern "C" void hs_pairing(const void* p, const void* q, void* o, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq12 r; pairing(r, ld<G1>(p, i), ld<G2>(q, i)); st(o, i, r); }
+}
+extern "C" void hs_constants(void* o) {
+    char* p = (char*)o;
+    Fq one = BN_C_ONE, r2 = BN_C_R2, r3 = BN_C_R3, two_inv = BN_C_TWO_INV, g1b = BN_C_G1_B, g1y = BN_C_G1_GEN_Y;
+    Fq2 g2b = BN_C_G2_B, tx = BN_C_TWIST_MUL_BY_Q_X, ty = BN_C_TWIST_MUL_BY_Q_Y, gx = BN_C_G2_GEN_X, gy = BN_C_G2_GEN_Y;
+    Fq2 f61[3] = {BN_C_FROB6_C1_1, BN_C_FROB6_C1_2, BN_C_FROB6_C1_3};
+    Fq2 f62[3] = {BN_C_FROB6_C2_1, BN_C_FROB6_C2_2, BN_C_FROB6_C2_3};
+    Fq2 f12[3] = {BN_C_FROB12_C1_1, BN_C_FROB12_C1_2, BN_C_FROB12_C1_3};
+#define PUT(x) do { memcpy(p, &(x), sizeof(x)); p += sizeof(x); } while (0)
+    PUT(one); PUT(r2); PUT(r3); PUT(two_inv); PUT(g1b); PUT(g1y); PUT(g2b); PUT(tx); PUT(ty);
+    PUT(f61); PUT(f62); PUT(f12); PUT(gx); PUT(gy);
+}

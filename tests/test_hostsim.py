@@ -1,0 +1,188 @@
+"""The device headers (paritytech-bn_b200/csrc/*.cuh), compiled for the host with the portable limb
+back end, against the C oracle: every formula, constant and branch of the CUDA code path is checked
+on the CPU; the GPU run then only has to confirm the PTX primitives and the kernels' data movement."""
+import ctypes
+import random
+
+import numpy as np
+import pytest
+
+from oracle import bn254_ref as o
+from oracle import c_oracle as c
+from tests import hostsim
+
+FQ, FQ2, FQ6, FQ12, G1, G2, ELL = 32, 64, 192, 384, 96, 192, 192
+rng = random.Random(20250)
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+def _b(x):
+    return np.frombuffer(o.to_bytes(x), dtype=np.uint8).copy()
+
+
+def rfq():
+    return rng.choice([0, 1, o.Q - 1, rng.randrange(o.Q), rng.randrange(o.Q), rng.randrange(o.Q)])
+
+
+def rand_elems(n_fq, n):
+    return np.concatenate([_b(tuple(rfq() for _ in range(n_fq))) for _ in range(n)])
+
+
+def hs_bin(name, a, b, unit):
+    n = a.size // unit
+    out = np.empty_like(a)
+    getattr(hostsim.lib(), "hs_" + name)(_p(a), _p(b), _p(out), ctypes.c_size_t(n))
+    return out
+
+
+def hs_un(name, a, unit):
+    n = a.size // unit
+    out = np.empty_like(a)
+    getattr(hostsim.lib(), "hs_" + name)(_p(a), _p(out), ctypes.c_size_t(n))
+    return out
+
+
+@pytest.mark.parametrize("name,unit,ref", [
+    ("fq_mul", FQ, c.fq_mul), ("fq_add", FQ, c.fq_add), ("fq_sub", FQ, c.fq_sub),
+    ("fq2_mul", FQ2, c.fq2_mul), ("fq6_mul", FQ6, c.fq6_mul), ("fq12_mul", FQ12, c.fq12_mul),
+    ("fq2_mul_alias", FQ2, c.fq2_mul), ("fq6_mul_alias", FQ6, c.fq6_mul), ("fq12_mul_alias", FQ12, c.fq12_mul),
+])
+def test_binary_field_ops(name, unit, ref):
+    n = 64
+    a, b = rand_elems(unit // 32, n), rand_elems(unit // 32, n)
+    assert hs_bin(name, a, b, unit).tobytes() == ref(a, b).tobytes()
+
+
+@pytest.mark.parametrize("name,unit,ref", [
+    ("fq2_sqr", FQ2, c.fq2_sqr), ("fq12_sqr", FQ12, c.fq12_sqr),
+    ("fq6_sqr", FQ6, lambda a: c.fq6_mul(a, a)),
+    ("fq2_mul_by_xi", FQ2, lambda a: c.fq2_mul(a, np.tile(_b(o.XI), a.size // FQ2))),
+    ("fq2_half", FQ2, lambda a: c.fq2_mul(a, np.tile(_b((o.TWO_INV, 0)), a.size // FQ2))),
+])
+def test_unary_field_ops(name, unit, ref):
+    a = rand_elems(unit // 32, 64)
+    assert hs_un(name, a, unit).tobytes() == ref(a).tobytes()
+
+
+def test_inversions_and_frobenius():
+    a = rand_elems(1, 40)
+    out = np.empty_like(a)
+    some = np.empty(40, dtype=np.uint8)
+    hostsim.lib().hs_fq_inv(_p(a), _p(out), _p(some), ctypes.c_size_t(40))
+    ro, rs = c.fq_inv(a)
+    assert (some == rs).all() and out.tobytes() == ro.tobytes()
+    a = np.concatenate([rand_elems(12, 6), _b(o.FQ12_ZERO)])
+    out = np.empty_like(a)
+    some = np.empty(7, dtype=np.uint8)
+    hostsim.lib().hs_fq12_inv(_p(a), _p(out), _p(some), ctypes.c_size_t(7))
+    ro, rs = c.fq12_inverse(a)
+    assert (some == rs).all() and some[6] == 0 and out.tobytes() == ro.tobytes()
+    for power in (1, 2, 3):
+        out = np.empty_like(a)
+        hostsim.lib().hs_fq12_frobenius(_p(a), ctypes.c_int(power), _p(out), ctypes.c_size_t(7))
+        assert out.tobytes() == c.fq12_frobenius(a, power).tobytes()
+
+
+def test_sparse_mul_and_cyclotomic():
+    f = rand_elems(12, 16)
+    ell = rand_elems(6, 16)
+    out = np.empty_like(f)
+    hostsim.lib().hs_fq12_mul_by_024(_p(f), _p(ell), _p(out), ctypes.c_size_t(16))
+    assert out.tobytes() == c.fq12_mul_by_024(f, ell).tobytes()
+    # cyclotomic-subgroup elements: easy part of the final exponentiation of random elements
+    g = rand_elems(12, 4)
+    cyc = np.concatenate([_b(o.fq12_final_exp_first_chunk(o.fq12_from_bytes(g[i * 384:(i + 1) * 384].tobytes()))) for i in range(4)])
+    assert hs_un("fq12_cyclotomic_sqr", cyc, FQ12).tobytes() == c.fq12_cyclotomic_squared(cyc).tobytes()
+    assert hs_un("fq12_exp_by_neg_z", cyc, FQ12).tobytes() == c.fq12_exp_by_neg_z(cyc).tobytes()
+    out = np.empty_like(g)
+    some = np.empty(4, dtype=np.uint8)
+    hostsim.lib().hs_final_exp(_p(g), _p(out), _p(some), ctypes.c_size_t(4))
+    ro, rs = c.final_exp(g)
+    assert (some == rs).all() and out.tobytes() == ro.tobytes()
+
+
+def _points(n, edge=True):
+    ks = [rng.randrange(1, o.R_ORDER) for _ in range(n)]
+    g1 = [o.g_mul(o.FQ_OPS, o.G1_ONE, k) for k in ks]
+    g2 = [o.g_mul(o.FQ2_OPS, o.G2_ONE, k + 1) for k in ks]
+    if edge:
+        g1 += [o.g_zero(o.FQ_OPS), o.G1_ONE]
+        g2 += [o.G2_ONE, o.g_zero(o.FQ2_OPS)]
+    return np.concatenate([_b(p) for p in g1]), np.concatenate([_b(p) for p in g2])
+
+
+def test_groups_and_scalar_mul():
+    p, q = _points(5)
+    n = p.size // G1
+    p2 = np.roll(p.reshape(n, G1), 1, axis=0).reshape(-1).copy()
+    q2 = np.roll(q.reshape(n, G2), 1, axis=0).reshape(-1).copy()
+    assert hs_bin("g1_add", p, p2, G1).tobytes() == c.g1_add(p, p2).tobytes()
+    assert hs_bin("g2_add", q, q2, G2).tobytes() == c.g2_add(q, q2).tobytes()
+    assert hs_bin("g1_add", p, p, G1).tobytes() == c.g1_add(p, p).tobytes()      # equal points -> double branch
+    assert hs_un("g1_double", p, G1).tobytes() == c.g1_double(p).tobytes()
+    assert hs_un("g2_double", q, G2).tobytes() == c.g2_double(q).tobytes()
+    assert hs_un("g1_normalize", p, G1).tobytes() == c.g1_normalize(p).tobytes()
+    assert hs_un("g2_normalize", q, G2).tobytes() == c.g2_normalize(q).tobytes()
+    ks = [0, 1, 2, o.R_ORDER - 1] + [rng.randrange(o.R_ORDER) for _ in range(n - 4)]
+    fr = np.concatenate([np.frombuffer(o.fr_to_bytes(k), dtype=np.uint8) for k in ks]).copy()
+    can = np.empty_like(fr)
+    hostsim.lib().hs_fr_to_canonical(_p(fr), _p(can), ctypes.c_size_t(n))
+    assert can.tobytes() == b"".join(k.to_bytes(32, "little") for k in ks)
+    out = np.empty_like(p)
+    hostsim.lib().hs_g1_mul(_p(p), _p(fr), _p(out), ctypes.c_size_t(n))
+    assert out.tobytes() == c.g1_mul(p, fr).tobytes()
+    out = np.empty_like(q)
+    hostsim.lib().hs_g2_mul(_p(q), _p(fr), _p(out), ctypes.c_size_t(n))
+    assert out.tobytes() == c.g2_mul(q, fr).tobytes()
+
+
+def test_precompute_miller_pairing(golden):
+    p, q = _points(3)
+    n = p.size // G1
+    pc = np.zeros(c.G2PRECOMP, dtype=np.uint8)
+    hostsim.lib().hs_g2_precompute.restype = ctypes.c_int
+    assert hostsim.lib().hs_g2_precompute(_p(q), _p(pc)) == 1
+    assert pc.tobytes() == c.g2_precompute(q[:G2]).tobytes()
+    out = np.empty(n * FQ12, dtype=np.uint8)
+    ok = np.empty(n, dtype=np.uint8)
+    hostsim.lib().hs_miller_loop(_p(q), _p(p), _p(out), _p(ok), ctypes.c_size_t(n))
+    ro, rok = c.miller_loop_many(q, p)
+    assert (ok == rok).all() and out.tobytes() == ro.tobytes()
+    hostsim.lib().hs_pairing(_p(p), _p(q), _p(out), ctypes.c_size_t(n))
+    assert out.tobytes() == c.pairing_many(p, q).tobytes()
+    # the reference's own golden pairing
+    v = golden["test_reduced_pairing"]
+    g1 = _b(o.g_mul(o.FQ_OPS, o.G1_ONE, int(v["g1_scalar"])))
+    g2 = _b(o.g_mul(o.FQ2_OPS, o.G2_ONE, int(v["g2_scalar"])))
+    one = np.empty(FQ12, dtype=np.uint8)
+    hostsim.lib().hs_pairing(_p(g1), _p(g2), _p(one), ctypes.c_size_t(1))
+    e = [int(x) for x in v["expected"]]
+    assert one.tobytes() == b"".join(o.fq_to_mont(x).to_bytes(32, "little") for x in e)
+
+
+def test_gt_pow():
+    a = rand_elems(12, 2)
+    ks = [rng.randrange(o.R_ORDER), 0]
+    fr = np.concatenate([np.frombuffer(o.fr_to_bytes(k), dtype=np.uint8) for k in ks]).copy()
+    out = np.empty_like(a)
+    hostsim.lib().hs_gt_pow(_p(a), _p(fr), _p(out), ctypes.c_size_t(2))
+    assert out.tobytes() == c.gt_pow(a, fr).tobytes()
+
+
+def test_constants_match_reference_literals(golden):
+    m = golden["montgomery_literals"]
+    buf = np.zeros(4096, dtype=np.uint8)
+    hostsim.lib().hs_constants(_p(buf))
+    raw = buf.tobytes()
+    vals = [int.from_bytes(raw[32 * i:32 * i + 32], "little") for i in range(40)]
+    exp = [int(m["fq"]["one"]), int(m["fq"]["rsquared"]), int(m["fq"]["rcubed"]), int(m["two_inv"]), int(m["g1_coeff_b"]),
+           int(m["g1_one_y"])] + [int(x) for x in m["g2_coeff_b"]] + [int(x) for x in m["twist_mul_by_q_x"]] + \
+          [int(x) for x in m["twist_mul_by_q_y"]]
+    for tab in ("fq6_frobenius_c1", "fq6_frobenius_c2", "fq12_frobenius_c1"):
+        for k in ("1", "2", "3"):
+            exp += [int(x) for x in m[tab][k]]
+    exp += [int(x) for x in m["g2_one"]["x"]] + [int(x) for x in m["g2_one"]["y"]]
+    assert vals[:len(exp)] == exp
