@@ -1,0 +1,152 @@
+/*
+ * bn254_b200 -- C ABI of the B200-native batched BN254 pairing engine.
+ *
+ * Drop-in boundary for the pairing surface of the `substrate-bn` crate (risc0/paritytech-bn).
+ * The reference has no FFI of its own; what makes this boundary possible is that every public
+ * type is #[repr(C)] down to U256([u128; 2]) (src/arith.rs:9-11), so the byte images below are
+ * exactly the Rust values:
+ *
+ *   Fr, Fq   32 B   little-endian 256-bit MONTGOMERY residue (R = 2^256), src/lib.rs:16-18, :125-127
+ *   Fq2      64 B   (c0, c1)                                              src/lib.rs:218-220
+ *   G1       96 B   Jacobian (x, y, z) of Fq                              src/lib.rs:322-324
+ *   G2      192 B   Jacobian (x, y, z) of Fq2                             src/lib.rs:469-471
+ *   Gt      384 B   Fq12 = 2 x Fq6 = 2 x 3 x Fq2                          src/lib.rs:584-586
+ *   G2Precomp image (export only): AffineG2 (128 B) + 87 x EllCoeffs{ell_0, ell_vw, ell_vv} (192 B)
+ *            = 16,832 B, field order of src/groups/mod.rs:566-577
+ *
+ * Every entry point is batched (pointer + count); the scalar functions of src/lib.rs are the n = 1
+ * calls.  Host-pointer entry points are synchronous.  `*_dev` entry points take DEVICE pointers
+ * (16-byte aligned) and enqueue on the context's stream without synchronising.
+ *
+ * Return codes: 0 = ok; > 0 = reference-level condition (documented per function);
+ *               < 0 = runtime failure (-1 bad argument, -2 CUDA error, -3 out of memory).
+ * Nothing aborts or throws across this boundary.  There is NO CPU fallback: without a CUDA device
+ * bn254_ctx_create fails and nothing else can be called.
+ */
+#ifndef BN254_B200_H
+#define BN254_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BN254_FR_BYTES 32
+#define BN254_FQ_BYTES 32
+#define BN254_G1_BYTES 96
+#define BN254_G2_BYTES 192
+#define BN254_GT_BYTES 384
+#define BN254_ELLCOEFFS_BYTES 192
+#define BN254_N_COEFFS 87
+#define BN254_G2PRECOMP_BYTES (128 + 87 * 192)
+
+#define BN254_OK 0
+#define BN254_ERR_TO_AFFINE 1 /* CurveError::ToAffineConversion, src/lib.rs:109-115, :629-630 */
+#define BN254_ERR_ARG (-1)
+#define BN254_ERR_CUDA (-2)
+#define BN254_ERR_NOMEM (-3)
+
+typedef struct bn254_ctx bn254_ctx;             /* one device + one stream + scratch */
+typedef struct bn254_g2precomp bn254_g2precomp; /* device-resident G2Precomp tables (engine-side handle;
+                                                   the reference's G2Precomp is private, src/lib.rs:7) */
+
+/* ---- context ------------------------------------------------------------------------------- */
+int bn254_ctx_create(int device, bn254_ctx** out);
+void bn254_ctx_destroy(bn254_ctx* ctx);
+int bn254_ctx_device(const bn254_ctx* ctx);
+/* the CUDA stream (cudaStream_t) all work of this context is enqueued on */
+void* bn254_ctx_stream(const bn254_ctx* ctx);
+int bn254_ctx_synchronize(bn254_ctx* ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches evidence) */
+uint64_t bn254_ctx_launch_count(const bn254_ctx* ctx);
+const char* bn254_last_error(void);
+const char* bn254_build_info(void);
+
+/* ---- pairing: src/lib.rs:611-613 `pairing(p: G1, q: G2) -> Gt`, n independent pairs ------------ */
+/* A pair with either point at infinity yields Gt::one() (src/groups/mod.rs:896). */
+int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_out, size_t n);
+int bn254_pairing_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_g2, void* d_gt_out, size_t n);
+
+/* ---- pairing_batch: src/lib.rs:615-623 `pairing_batch(&[(G1, G2)]) -> Gt` ---------------------- */
+/* n_checks independent products of pairs_per_check pairs each (pair j of check i at index
+ * i*pairs_per_check + j), ONE final exponentiation per check.  Pairs with a point at infinity are
+ * skipped; a check with no remaining pair yields one (src/groups/mod.rs:904-926).
+ * gt_out (n_checks x 384 B) and is_one (n_checks bytes: result == Gt::one()) may each be NULL. */
+int bn254_pairing_product_many(bn254_ctx* ctx, const void* g1, const void* g2, size_t pairs_per_check,
+                               size_t n_checks, void* gt_out, uint8_t* is_one);
+int bn254_pairing_product_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_g2, size_t pairs_per_check,
+                                   size_t n_checks, void* d_gt_out, uint8_t* d_is_one);
+
+/* ---- miller_loop_batch: src/lib.rs:625-633 `miller_loop_batch(&[(G2, G1)]) -> Result<Gt, _>` ---- */
+/* NOTE the (G2, G1) order.  One un-exponentiated product over all n pairs.  Returns
+ * BN254_ERR_TO_AFFINE if any point is at infinity (gt_out untouched), like the reference. */
+int bn254_miller_loop_batch(bn254_ctx* ctx, const void* g2, const void* g1, size_t n, void* gt_out);
+/* n independent single-pair Miller loops (pre-final-exponentiation values); ok[i] = 0 and gt = one
+ * where a point is at infinity.  ok may be NULL. */
+int bn254_miller_loop_many(bn254_ctx* ctx, const void* g2, const void* g1, void* gt_out, uint8_t* ok, size_t n);
+int bn254_miller_loop_many_dev(bn254_ctx* ctx, const void* d_g2, const void* d_g1, void* d_gt_out, uint8_t* d_ok,
+                               size_t n);
+
+/* ---- Gt: src/lib.rs:584-609 -------------------------------------------------------------------- */
+/* Gt::final_exponentiation -> Option<Gt>: some[i] = 0 (and gt_out = 0) iff the input is zero */
+int bn254_final_exp_many(bn254_ctx* ctx, const void* gt_in, void* gt_out, uint8_t* some, size_t n);
+int bn254_final_exp_many_dev(bn254_ctx* ctx, const void* d_gt_in, void* d_gt_out, uint8_t* d_some, size_t n);
+int bn254_gt_mul_many(bn254_ctx* ctx, const void* a, const void* b, void* out, size_t n);     /* Gt * Gt   */
+int bn254_gt_pow_many(bn254_ctx* ctx, const void* a, const void* fr, void* out, size_t n);    /* Gt::pow   */
+int bn254_gt_inverse_many(bn254_ctx* ctx, const void* a, void* out, uint8_t* some, size_t n); /* Gt::inverse */
+int bn254_gt_eq_many(bn254_ctx* ctx, const void* a, const void* b, uint8_t* eq, size_t n);    /* PartialEq */
+
+/* ---- G1 * Fr, G2 * Fr: src/lib.rs:425-431, :576-582 -------------------------------------------- */
+/* Fr is the crate's Montgomery image; the kernel de-Montgomeries it (src/groups/mod.rs:279).
+ * The result is the reference's own Jacobian representative (same add/double sequence). */
+int bn254_g1_mul_many(bn254_ctx* ctx, const void* g1, const void* fr, void* g1_out, size_t n);
+int bn254_g2_mul_many(bn254_ctx* ctx, const void* g2, const void* fr, void* g2_out, size_t n);
+int bn254_g1_mul_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_fr, void* d_out, size_t n);
+int bn254_g2_mul_many_dev(bn254_ctx* ctx, const void* d_g2, const void* d_fr, void* d_out, size_t n);
+/* Group::normalize, src/lib.rs:391-398, :542-549: z -> one (infinity untouched) */
+int bn254_g1_normalize_many(bn254_ctx* ctx, const void* g1, void* g1_out, size_t n);
+int bn254_g2_normalize_many(bn254_ctx* ctx, const void* g2, void* g2_out, size_t n);
+
+/* ---- shared G2Precomp: src/groups/mod.rs:573-577, :701-728 ------------------------------------- */
+/* Precompute the 87 line-coefficient triples of n G2 points once; the tables stay on the device.
+ * Returns BN254_ERR_TO_AFFINE if a point is at infinity. */
+int bn254_g2_precompute(bn254_ctx* ctx, const void* g2, size_t n, bn254_g2precomp** out);
+void bn254_g2precomp_destroy(bn254_g2precomp* pc);
+size_t bn254_g2precomp_count(const bn254_g2precomp* pc);
+/* copy table i back in the reference's G2Precomp field order (BN254_G2PRECOMP_BYTES) */
+int bn254_g2precomp_export(bn254_ctx* ctx, const bn254_g2precomp* pc, size_t i, void* out);
+/* Groth16-shaped product checks with shared tables: check i multiplies
+ *   prod_{j < m}  e(g1_shared[i*m + j], table j)   (m = bn254_g2precomp_count(pc))
+ *   prod_{j < v}  e(g1_var[i*v + j], g2_var[i*v + j])
+ * with one shared squaring chain and one final exponentiation.  Infinity pairs are skipped. */
+int bn254_pairing_product_precomp_many(bn254_ctx* ctx, const bn254_g2precomp* pc, const void* g1_shared,
+                                       const void* g1_var, const void* g2_var, size_t v, size_t n_checks,
+                                       void* gt_out, uint8_t* is_one);
+int bn254_pairing_product_precomp_many_dev(bn254_ctx* ctx, const bn254_g2precomp* pc, const void* d_g1_shared,
+                                           const void* d_g1_var, const void* d_g2_var, size_t v, size_t n_checks,
+                                           void* d_gt_out, uint8_t* d_is_one);
+
+/* ---- one product sharded over several devices -------------------------------------- */
+/* prod_i e(g1[i], g2[i]) over n pairs split by index range across n_ctx contexts (one per GPU):
+ * each device reduces its range to one un-exponentiated Fq12 (384 B), the partials are gathered to
+ * ctxs[0] by peer copy, multiplied, and exponentiated once.  Same skip semantics as pairing_batch. */
+int bn254_pairing_product_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1, const void* g2, size_t n,
+                                  void* gt_out, uint8_t* is_one);
+
+/* ---- field-level test hooks (parity tests of the arithmetic kernels) ---------------------------- */
+/* op: 0 = Fq mul, 1 = Fq add, 2 = Fq sub, 3 = Fq2 mul, 4 = Fq2 sqr, 5 = Fq6 mul, 6 = Fq12 mul,
+ *     7 = Fq12 sqr, 8 = Fq12 cyclotomic_squared, 9 = Fq inverse (b ignored) */
+int bn254_field_op_many(bn254_ctx* ctx, int op, const void* a, const void* b, void* out, size_t n);
+
+/* ---- roofline microbenchmarks (register-only; report via bench.py) ------------------------------ */
+/* kind: 0 = IMAD (mad.lo.u32) chains, 1 = IMAD.WIDE (mad.wide.u32) chains, 2 = back-to-back Fq
+ * Montgomery multiplications.  Returns elapsed milliseconds for `iters` iterations x `ilp`
+ * independent chains per thread over grid*block threads; *ops receives the op count. */
+int bn254_microbench(bn254_ctx* ctx, int kind, int grid, int block, int iters, double* ms, double* ops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BN254_B200_H */

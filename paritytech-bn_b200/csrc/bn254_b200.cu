@@ -1,0 +1,592 @@
+// C-ABI implementation (include/bn254_b200.h): contexts, device buffers, kernel launches.
+// Every entry point launches CUDA kernels; there is no CPU arithmetic path in this library.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/bn254_b200.h"
+#include "bn254_kernels.cuh"
+
+using namespace bn;
+
+static_assert(sizeof(Fq) == 32 && sizeof(Fq2) == 64 && sizeof(Fq12) == 384, "repr(C) sizes");
+static_assert(sizeof(G1) == 96 && sizeof(G2) == 192 && sizeof(EllCoeffs) == 192, "repr(C) sizes");
+static_assert(sizeof(AffG2) == 128 && sizeof(AffG1) == 64, "repr(C) sizes");
+
+static thread_local std::string g_err;
+static int fail(int code, const char* what, cudaError_t e = cudaSuccess) {
+    g_err = what;
+    if (e != cudaSuccess) { g_err += ": "; g_err += cudaGetErrorString(e); }
+    return code;
+}
+#define CU(call) do { cudaError_t _e = (call); if (_e != cudaSuccess) return fail(BN254_ERR_CUDA, #call, _e); } while (0)
+
+struct bn254_ctx {
+    int device;
+    cudaStream_t stream;
+    std::atomic<uint64_t> launches;
+};
+struct bn254_g2precomp {
+    int device;
+    size_t n;
+    uint4* tab;     // [(c*12 + w) * n + j]
+    AffG2* q_aff;   // [n]
+};
+
+// RAII device buffer on the context's device
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t bytes) {
+        if (bytes == 0) bytes = 16;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e != cudaSuccess) { p = nullptr; return fail(BN254_ERR_NOMEM, "cudaMalloc", e); }
+        return 0;
+    }
+    template <class T> T* as() { return reinterpret_cast<T*>(p); }
+};
+#define TRY(x) do { int _r = (x); if (_r != 0) return _r; } while (0)
+
+static inline unsigned grid_for(size_t n) { return (unsigned)((n + BN_BLOCK - 1) / BN_BLOCK); }
+#define LAUNCH(ctx, kernel, n, ...)                                                        \
+    do {                                                                                   \
+        if ((n) > 0) {                                                                     \
+            kernel<<<grid_for(n), BN_BLOCK, 0, (ctx)->stream>>>(__VA_ARGS__);              \
+            (ctx)->launches.fetch_add(1);                                                  \
+            CU(cudaGetLastError());                                                        \
+        }                                                                                  \
+    } while (0)
+
+static int use(bn254_ctx* ctx) {
+    if (!ctx) return fail(BN254_ERR_ARG, "null context");
+    CU(cudaSetDevice(ctx->device));
+    return 0;
+}
+static int h2d(bn254_ctx* ctx, void* d, const void* h, size_t bytes) {
+    if (bytes) CU(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return 0;
+}
+static int d2h(bn254_ctx* ctx, void* h, const void* d, size_t bytes) {
+    if (bytes) CU(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return 0;
+}
+
+extern "C" {
+
+const char* bn254_last_error(void) { return g_err.c_str(); }
+const char* bn254_build_info(void) {
+    static char buf[160];
+    snprintf(buf, sizeof buf, "bn254_b200 sm_100a block=%d min_blocks=%d cuda=%d", BN_BLOCK, BN_MIN_BLOCKS, CUDART_VERSION);
+    return buf;
+}
+
+int bn254_ctx_create(int device, bn254_ctx** out) {
+    if (!out) return fail(BN254_ERR_ARG, "null out");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) return fail(BN254_ERR_CUDA, "no CUDA device (this library has no CPU fallback)", e);
+    if (device < 0 || device >= count) return fail(BN254_ERR_ARG, "bad device index");
+    CU(cudaSetDevice(device));
+    bn254_ctx* c = new (std::nothrow) bn254_ctx();
+    if (!c) return fail(BN254_ERR_NOMEM, "ctx alloc");
+    c->device = device;
+    c->launches = 0;
+    e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { delete c; return fail(BN254_ERR_CUDA, "cudaStreamCreate", e); }
+    // deep call chains (Fq12 -> Fq6 -> Fq2 noinline bodies) need more than the default stack
+    cudaDeviceSetLimit(cudaLimitStackSize, 16 * 1024);
+    *out = c;
+    return 0;
+}
+void bn254_ctx_destroy(bn254_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+int bn254_ctx_device(const bn254_ctx* ctx) { return ctx ? ctx->device : -1; }
+void* bn254_ctx_stream(const bn254_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+int bn254_ctx_synchronize(bn254_ctx* ctx) {
+    TRY(use(ctx));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+uint64_t bn254_ctx_launch_count(const bn254_ctx* ctx) { return ctx ? ctx->launches.load() : 0; }
+
+// ---------------------------------------------------------------------------------------------
+// pairing
+// ---------------------------------------------------------------------------------------------
+int bn254_pairing_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_g2, void* d_gt_out, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!d_g1 || !d_g2 || !d_gt_out) return fail(BN254_ERR_ARG, "null pointer");
+    // Miller values are written to the output buffer and exponentiated in place
+    LAUNCH(ctx, k_miller_many, n, (const G2*)d_g2, (const G1*)d_g1, (Fq12*)d_gt_out, (uint8_t*)nullptr, n);
+    LAUNCH(ctx, k_final_exp_many, n, (const Fq12*)d_gt_out, (Fq12*)d_gt_out, (uint8_t*)nullptr, (uint8_t*)nullptr, n);
+    return 0;
+}
+int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_out, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!g1 || !g2 || !gt_out) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf a, b, o;
+    TRY(a.alloc(n * sizeof(G1))); TRY(b.alloc(n * sizeof(G2))); TRY(o.alloc(n * sizeof(Fq12)));
+    TRY(h2d(ctx, a.p, g1, n * sizeof(G1)));
+    TRY(h2d(ctx, b.p, g2, n * sizeof(G2)));
+    TRY(bn254_pairing_many_dev(ctx, a.p, b.p, o.p, n));
+    TRY(d2h(ctx, gt_out, o.p, n * sizeof(Fq12)));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int bn254_miller_loop_many_dev(bn254_ctx* ctx, const void* d_g2, const void* d_g1, void* d_gt_out, uint8_t* d_ok, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!d_g1 || !d_g2 || !d_gt_out) return fail(BN254_ERR_ARG, "null pointer");
+    LAUNCH(ctx, k_miller_many, n, (const G2*)d_g2, (const G1*)d_g1, (Fq12*)d_gt_out, d_ok, n);
+    return 0;
+}
+int bn254_miller_loop_many(bn254_ctx* ctx, const void* g2, const void* g1, void* gt_out, uint8_t* ok, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!g1 || !g2 || !gt_out) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf a, b, o, k;
+    TRY(a.alloc(n * sizeof(G1))); TRY(b.alloc(n * sizeof(G2))); TRY(o.alloc(n * sizeof(Fq12))); TRY(k.alloc(n));
+    TRY(h2d(ctx, a.p, g1, n * sizeof(G1)));
+    TRY(h2d(ctx, b.p, g2, n * sizeof(G2)));
+    TRY(bn254_miller_loop_many_dev(ctx, b.p, a.p, o.p, k.as<uint8_t>(), n));
+    TRY(d2h(ctx, gt_out, o.p, n * sizeof(Fq12)));
+    if (ok) TRY(d2h(ctx, ok, k.p, n));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// product checks (pairing_batch) and miller_loop_batch
+// ---------------------------------------------------------------------------------------------
+// reduce n Fq12 values in `a` to one product; `b` is scratch of >= (n+1)/2 elements.  Result pointer returned.
+static int tree_product(bn254_ctx* ctx, Fq12* a, Fq12* b, size_t n, Fq12** result) {
+    Fq12 *src = a, *dst = b;
+    while (n > 1) {
+        size_t n_out = (n + 1) / 2;
+        LAUNCH(ctx, k_fq12_pair_product, n_out, (const Fq12*)src, n, dst);
+        n = n_out;
+        Fq12* t = src; src = dst; dst = t;
+    }
+    *result = src;
+    return 0;
+}
+
+// Miller products of n_checks checks into d_f (n_checks x Fq12); shared tables optional
+static int miller_products_dev(bn254_ctx* ctx, const G1* d_g1v, const G2* d_g2v, size_t v, const G1* d_g1s,
+                               const bn254_g2precomp* pc, size_t n_checks, Fq12* d_f) {
+    size_t m = pc ? pc->n : 0;
+    const uint4* tab = pc ? pc->tab : nullptr;
+    if (m > 8) return fail(BN254_ERR_ARG, "at most 8 shared tables per check");
+    if (v <= 1 && m <= 4) {
+        LAUNCH(ctx, (k_miller_product<1, 4>), n_checks, d_g1v, d_g2v, (int)v, d_g1s, tab, (int)m, d_f, n_checks);
+    } else if (v <= 4 && m <= 4) {
+        LAUNCH(ctx, (k_miller_product<4, 4>), n_checks, d_g1v, d_g2v, (int)v, d_g1s, tab, (int)m, d_f, n_checks);
+    } else if (v <= 8) {
+        LAUNCH(ctx, (k_miller_product<8, 8>), n_checks, d_g1v, d_g2v, (int)v, d_g1s, tab, (int)m, d_f, n_checks);
+    } else {
+        // many pairs per check: independent Miller loops, then a per-check product (same field element)
+        if (m != 0) return fail(BN254_ERR_ARG, "more than 8 variable pairs cannot be combined with shared tables");
+        DevBuf tmp;
+        TRY(tmp.alloc(n_checks * v * sizeof(Fq12)));
+        LAUNCH(ctx, k_miller_many, n_checks * v, d_g2v, d_g1v, tmp.as<Fq12>(), (uint8_t*)nullptr, n_checks * v);
+        LAUNCH(ctx, k_fq12_group_product, n_checks, (const Fq12*)tmp.as<Fq12>(), v, d_f, n_checks);
+        CU(cudaStreamSynchronize(ctx->stream));   // tmp is freed on return
+    }
+    return 0;
+}
+
+int bn254_pairing_product_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_g2, size_t pairs_per_check,
+                                   size_t n_checks, void* d_gt_out, uint8_t* d_is_one) {
+    TRY(use(ctx));
+    if (n_checks == 0) return 0;
+    if (pairs_per_check && (!d_g1 || !d_g2)) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf f;
+    Fq12* d_f = (Fq12*)d_gt_out;
+    if (!d_f) { TRY(f.alloc(n_checks * sizeof(Fq12))); d_f = f.as<Fq12>(); }
+    TRY(miller_products_dev(ctx, (const G1*)d_g1, (const G2*)d_g2, pairs_per_check, nullptr, nullptr, n_checks, d_f));
+    LAUNCH(ctx, k_final_exp_many, n_checks, (const Fq12*)d_f, d_gt_out ? d_f : (Fq12*)nullptr, (uint8_t*)nullptr, d_is_one, n_checks);
+    if (!d_gt_out) CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int bn254_pairing_product_many(bn254_ctx* ctx, const void* g1, const void* g2, size_t pairs_per_check, size_t n_checks,
+                               void* gt_out, uint8_t* is_one) {
+    TRY(use(ctx));
+    if (n_checks == 0) return 0;
+    size_t n = pairs_per_check * n_checks;
+    if (n && (!g1 || !g2)) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf a, b, o, k;
+    TRY(a.alloc(n * sizeof(G1))); TRY(b.alloc(n * sizeof(G2))); TRY(o.alloc(n_checks * sizeof(Fq12))); TRY(k.alloc(n_checks));
+    TRY(h2d(ctx, a.p, g1, n * sizeof(G1)));
+    TRY(h2d(ctx, b.p, g2, n * sizeof(G2)));
+    TRY(bn254_pairing_product_many_dev(ctx, a.p, b.p, pairs_per_check, n_checks, o.p, k.as<uint8_t>()));
+    if (gt_out) TRY(d2h(ctx, gt_out, o.p, n_checks * sizeof(Fq12)));
+    if (is_one) TRY(d2h(ctx, is_one, k.p, n_checks));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int bn254_miller_loop_batch(bn254_ctx* ctx, const void* g2, const void* g1, size_t n, void* gt_out) {
+    TRY(use(ctx));
+    if (!gt_out) return fail(BN254_ERR_ARG, "null pointer");
+    if (n == 0) {   // empty product: Fq12::one(), src/groups/mod.rs:610
+        DevBuf o;
+        TRY(o.alloc(sizeof(Fq12)));
+        LAUNCH(ctx, (k_miller_product<1, 4>), 1, (const G1*)nullptr, (const G2*)nullptr, 0, (const G1*)nullptr,
+               (const uint4*)nullptr, 0, o.as<Fq12>(), (size_t)1);
+        TRY(d2h(ctx, gt_out, o.p, sizeof(Fq12)));
+        CU(cudaStreamSynchronize(ctx->stream));
+        return 0;
+    }
+    if (!g1 || !g2) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf a, b, f, s, k;
+    TRY(a.alloc(n * sizeof(G1))); TRY(b.alloc(n * sizeof(G2))); TRY(f.alloc(n * sizeof(Fq12)));
+    TRY(s.alloc(((n + 1) / 2) * sizeof(Fq12))); TRY(k.alloc(n));
+    TRY(h2d(ctx, a.p, g1, n * sizeof(G1)));
+    TRY(h2d(ctx, b.p, g2, n * sizeof(G2)));
+    LAUNCH(ctx, k_miller_many, n, b.as<G2>(), a.as<G1>(), f.as<Fq12>(), k.as<uint8_t>(), n);
+    std::vector<uint8_t> ok(n);
+    TRY(d2h(ctx, ok.data(), k.p, n));
+    CU(cudaStreamSynchronize(ctx->stream));
+    for (size_t i = 0; i < n; i++)
+        if (!ok[i]) return BN254_ERR_TO_AFFINE;   // Err(CurveError::ToAffineConversion), src/lib.rs:629-630
+    Fq12* res = nullptr;
+    TRY(tree_product(ctx, f.as<Fq12>(), s.as<Fq12>(), n, &res));
+    TRY(d2h(ctx, gt_out, res, sizeof(Fq12)));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Gt
+// ---------------------------------------------------------------------------------------------
+int bn254_final_exp_many_dev(bn254_ctx* ctx, const void* d_in, void* d_out, uint8_t* d_some, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!d_in || !d_out) return fail(BN254_ERR_ARG, "null pointer");
+    LAUNCH(ctx, k_final_exp_many, n, (const Fq12*)d_in, (Fq12*)d_out, d_some, (uint8_t*)nullptr, n);
+    return 0;
+}
+int bn254_final_exp_many(bn254_ctx* ctx, const void* gt_in, void* gt_out, uint8_t* some, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!gt_in || !gt_out) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf a, o, k;
+    TRY(a.alloc(n * sizeof(Fq12))); TRY(o.alloc(n * sizeof(Fq12))); TRY(k.alloc(n));
+    TRY(h2d(ctx, a.p, gt_in, n * sizeof(Fq12)));
+    TRY(bn254_final_exp_many_dev(ctx, a.p, o.p, k.as<uint8_t>(), n));
+    TRY(d2h(ctx, gt_out, o.p, n * sizeof(Fq12)));
+    if (some) TRY(d2h(ctx, some, k.p, n));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int bn254_gt_mul_many(bn254_ctx* ctx, const void* a, const void* b, void* out, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!a || !b || !out) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf x, y, o;
+    TRY(x.alloc(n * sizeof(Fq12))); TRY(y.alloc(n * sizeof(Fq12))); TRY(o.alloc(n * sizeof(Fq12)));
+    TRY(h2d(ctx, x.p, a, n * sizeof(Fq12))); TRY(h2d(ctx, y.p, b, n * sizeof(Fq12)));
+    LAUNCH(ctx, k_gt_mul, n, x.as<Fq12>(), y.as<Fq12>(), o.as<Fq12>(), n);
+    TRY(d2h(ctx, out, o.p, n * sizeof(Fq12)));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int bn254_gt_pow_many(bn254_ctx* ctx, const void* a, const void* fr, void* out, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!a || !fr || !out) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf x, y, o;
+    TRY(x.alloc(n * sizeof(Fq12))); TRY(y.alloc(n * sizeof(Fq))); TRY(o.alloc(n * sizeof(Fq12)));
+    TRY(h2d(ctx, x.p, a, n * sizeof(Fq12))); TRY(h2d(ctx, y.p, fr, n * sizeof(Fq)));
+    LAUNCH(ctx, k_gt_pow, n, x.as<Fq12>(), y.as<Fq>(), o.as<Fq12>(), n);
+    TRY(d2h(ctx, out, o.p, n * sizeof(Fq12)));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int bn254_gt_inverse_many(bn254_ctx* ctx, const void* a, void* out, uint8_t* some, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!a || !out) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf x, o, k;
+    TRY(x.alloc(n * sizeof(Fq12))); TRY(o.alloc(n * sizeof(Fq12))); TRY(k.alloc(n));
+    TRY(h2d(ctx, x.p, a, n * sizeof(Fq12)));
+    LAUNCH(ctx, k_gt_inverse, n, x.as<Fq12>(), o.as<Fq12>(), k.as<uint8_t>(), n);
+    TRY(d2h(ctx, out, o.p, n * sizeof(Fq12)));
+    if (some) TRY(d2h(ctx, some, k.p, n));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int bn254_gt_eq_many(bn254_ctx* ctx, const void* a, const void* b, uint8_t* eq, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!a || !b || !eq) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf x, y, k;
+    TRY(x.alloc(n * sizeof(Fq12))); TRY(y.alloc(n * sizeof(Fq12))); TRY(k.alloc(n));
+    TRY(h2d(ctx, x.p, a, n * sizeof(Fq12))); TRY(h2d(ctx, y.p, b, n * sizeof(Fq12)));
+    LAUNCH(ctx, k_gt_eq, n, x.as<Fq12>(), y.as<Fq12>(), k.as<uint8_t>(), n);
+    TRY(d2h(ctx, eq, k.p, n));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// G1 * Fr, G2 * Fr, normalize
+// ---------------------------------------------------------------------------------------------
+int bn254_g1_mul_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_fr, void* d_out, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!d_g1 || !d_fr || !d_out) return fail(BN254_ERR_ARG, "null pointer");
+    LAUNCH(ctx, k_jac_mul<FqOps>, n, (const G1*)d_g1, (const Fq*)d_fr, (G1*)d_out, n);
+    return 0;
+}
+int bn254_g2_mul_many_dev(bn254_ctx* ctx, const void* d_g2, const void* d_fr, void* d_out, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!d_g2 || !d_fr || !d_out) return fail(BN254_ERR_ARG, "null pointer");
+    LAUNCH(ctx, k_jac_mul<Fq2Ops>, n, (const G2*)d_g2, (const Fq*)d_fr, (G2*)d_out, n);
+    return 0;
+}
+}  // extern "C"
+template <class P>
+static int scalar_mul_host(bn254_ctx* ctx, const void* p, const void* fr, void* out, size_t n,
+                           int (*dev)(bn254_ctx*, const void*, const void*, void*, size_t)) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!p || !fr || !out) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf a, b, o;
+    TRY(a.alloc(n * sizeof(P))); TRY(b.alloc(n * sizeof(Fq))); TRY(o.alloc(n * sizeof(P)));
+    TRY(h2d(ctx, a.p, p, n * sizeof(P))); TRY(h2d(ctx, b.p, fr, n * sizeof(Fq)));
+    TRY(dev(ctx, a.p, b.p, o.p, n));
+    TRY(d2h(ctx, out, o.p, n * sizeof(P)));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+extern "C" {
+int bn254_g1_mul_many(bn254_ctx* ctx, const void* g1, const void* fr, void* out, size_t n) {
+    return scalar_mul_host<G1>(ctx, g1, fr, out, n, bn254_g1_mul_many_dev);
+}
+int bn254_g2_mul_many(bn254_ctx* ctx, const void* g2, const void* fr, void* out, size_t n) {
+    return scalar_mul_host<G2>(ctx, g2, fr, out, n, bn254_g2_mul_many_dev);
+}
+int bn254_g1_normalize_many(bn254_ctx* ctx, const void* g1, void* out, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!g1 || !out) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf a, o;
+    TRY(a.alloc(n * sizeof(G1))); TRY(o.alloc(n * sizeof(G1)));
+    TRY(h2d(ctx, a.p, g1, n * sizeof(G1)));
+    LAUNCH(ctx, k_jac_normalize<FqOps>, n, a.as<G1>(), o.as<G1>(), n);
+    TRY(d2h(ctx, out, o.p, n * sizeof(G1)));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int bn254_g2_normalize_many(bn254_ctx* ctx, const void* g2, void* out, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!g2 || !out) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf a, o;
+    TRY(a.alloc(n * sizeof(G2))); TRY(o.alloc(n * sizeof(G2)));
+    TRY(h2d(ctx, a.p, g2, n * sizeof(G2)));
+    LAUNCH(ctx, k_jac_normalize<Fq2Ops>, n, a.as<G2>(), o.as<G2>(), n);
+    TRY(d2h(ctx, out, o.p, n * sizeof(G2)));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// shared G2Precomp tables
+// ---------------------------------------------------------------------------------------------
+void bn254_g2precomp_destroy(bn254_g2precomp* pc) {
+    if (!pc) return;
+    cudaSetDevice(pc->device);
+    if (pc->tab) cudaFree(pc->tab);
+    if (pc->q_aff) cudaFree(pc->q_aff);
+    delete pc;
+}
+size_t bn254_g2precomp_count(const bn254_g2precomp* pc) { return pc ? pc->n : 0; }
+int bn254_g2_precompute(bn254_ctx* ctx, const void* g2, size_t n, bn254_g2precomp** out) {
+    TRY(use(ctx));
+    if (!out || !g2 || n == 0) return fail(BN254_ERR_ARG, "bad argument");
+    bn254_g2precomp* pc = new (std::nothrow) bn254_g2precomp();
+    if (!pc) return fail(BN254_ERR_NOMEM, "precomp alloc");
+    pc->device = ctx->device; pc->n = n; pc->tab = nullptr; pc->q_aff = nullptr;
+    DevBuf a, bad;
+    int rc = a.alloc(n * sizeof(G2));
+    if (rc == 0) rc = bad.alloc(sizeof(int));
+    if (rc == 0 && cudaMalloc((void**)&pc->tab, (size_t)BN254_N_COEFFS * 12 * n * sizeof(uint4)) != cudaSuccess) rc = fail(BN254_ERR_NOMEM, "cudaMalloc table");
+    if (rc == 0 && cudaMalloc((void**)&pc->q_aff, n * sizeof(AffG2)) != cudaSuccess) rc = fail(BN254_ERR_NOMEM, "cudaMalloc q");
+    if (rc != 0) { bn254_g2precomp_destroy(pc); return rc; }
+    int h_bad = 0;
+    auto body = [&]() -> int {
+        CU(cudaMemsetAsync(bad.p, 0, sizeof(int), ctx->stream));
+        TRY(h2d(ctx, a.p, g2, n * sizeof(G2)));
+        LAUNCH(ctx, k_g2_precompute, n, a.as<G2>(), pc->tab, pc->q_aff, bad.as<int>(), n);
+        TRY(d2h(ctx, &h_bad, bad.p, sizeof(int)));
+        CU(cudaStreamSynchronize(ctx->stream));
+        return 0;
+    };
+    rc = body();
+    if (rc == 0 && h_bad) rc = BN254_ERR_TO_AFFINE;
+    if (rc != 0) { bn254_g2precomp_destroy(pc); return rc; }
+    *out = pc;
+    return 0;
+}
+int bn254_g2precomp_export(bn254_ctx* ctx, const bn254_g2precomp* pc, size_t i, void* out) {
+    TRY(use(ctx));
+    if (!pc || !out || i >= pc->n) return fail(BN254_ERR_ARG, "bad argument");
+    uint8_t* o = (uint8_t*)out;
+    TRY(d2h(ctx, o, pc->q_aff + i, sizeof(AffG2)));
+    // gather the strided 16-byte words of table i: one 2D copy (pitch = n*16 bytes)
+    CU(cudaMemcpy2DAsync(o + sizeof(AffG2), sizeof(uint4), pc->tab + i, pc->n * sizeof(uint4), sizeof(uint4),
+                         (size_t)BN254_N_COEFFS * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int bn254_pairing_product_precomp_many_dev(bn254_ctx* ctx, const bn254_g2precomp* pc, const void* d_g1s, const void* d_g1v,
+                                           const void* d_g2v, size_t v, size_t n_checks, void* d_gt_out, uint8_t* d_is_one) {
+    TRY(use(ctx));
+    if (n_checks == 0) return 0;
+    if (pc && pc->device != ctx->device) return fail(BN254_ERR_ARG, "precomp tables live on another device");
+    if ((pc && !d_g1s) || (v && (!d_g1v || !d_g2v))) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf f;
+    Fq12* d_f = (Fq12*)d_gt_out;
+    if (!d_f) { TRY(f.alloc(n_checks * sizeof(Fq12))); d_f = f.as<Fq12>(); }
+    TRY(miller_products_dev(ctx, (const G1*)d_g1v, (const G2*)d_g2v, v, (const G1*)d_g1s, pc, n_checks, d_f));
+    LAUNCH(ctx, k_final_exp_many, n_checks, (const Fq12*)d_f, d_gt_out ? d_f : (Fq12*)nullptr, (uint8_t*)nullptr, d_is_one, n_checks);
+    if (!d_gt_out) CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int bn254_pairing_product_precomp_many(bn254_ctx* ctx, const bn254_g2precomp* pc, const void* g1_shared, const void* g1_var,
+                                       const void* g2_var, size_t v, size_t n_checks, void* gt_out, uint8_t* is_one) {
+    TRY(use(ctx));
+    if (n_checks == 0) return 0;
+    size_t m = pc ? pc->n : 0;
+    if ((m && !g1_shared) || (v && (!g1_var || !g2_var))) return fail(BN254_ERR_ARG, "null pointer");
+    DevBuf s, a, b, o, k;
+    TRY(s.alloc(n_checks * m * sizeof(G1))); TRY(a.alloc(n_checks * v * sizeof(G1))); TRY(b.alloc(n_checks * v * sizeof(G2)));
+    TRY(o.alloc(n_checks * sizeof(Fq12))); TRY(k.alloc(n_checks));
+    TRY(h2d(ctx, s.p, g1_shared, n_checks * m * sizeof(G1)));
+    TRY(h2d(ctx, a.p, g1_var, n_checks * v * sizeof(G1)));
+    TRY(h2d(ctx, b.p, g2_var, n_checks * v * sizeof(G2)));
+    TRY(bn254_pairing_product_precomp_many_dev(ctx, pc, s.p, a.p, b.p, v, n_checks, o.p, k.as<uint8_t>()));
+    if (gt_out) TRY(d2h(ctx, gt_out, o.p, n_checks * sizeof(Fq12)));
+    if (is_one) TRY(d2h(ctx, is_one, k.p, n_checks));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// one product sharded over several devices: 384-byte partials gathered by peer copy (no NCCL)
+// ---------------------------------------------------------------------------------------------
+int bn254_pairing_product_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1, const void* g2, size_t n, void* gt_out,
+                                  uint8_t* is_one) {
+    if (!ctxs || n_ctx == 0) return fail(BN254_ERR_ARG, "no contexts");
+    for (size_t d = 0; d < n_ctx; d++) if (!ctxs[d]) return fail(BN254_ERR_ARG, "null context");
+    if (n && (!g1 || !g2)) return fail(BN254_ERR_ARG, "null pointer");
+    struct Shard { DevBuf a, b, f, s; Fq12* res = nullptr; size_t lo = 0, cnt = 0; };
+    std::vector<Shard> sh(n_ctx);
+    bn254_ctx* c0 = ctxs[0];
+    TRY(use(c0));
+    DevBuf partials, scratch, out, flag;
+    TRY(partials.alloc(n_ctx * sizeof(Fq12))); TRY(scratch.alloc(n_ctx * sizeof(Fq12)));
+    TRY(out.alloc(sizeof(Fq12))); TRY(flag.alloc(1));
+    // phase 1: every device reduces its index range to one Miller product (all launches asynchronous)
+    for (size_t d = 0; d < n_ctx; d++) {
+        bn254_ctx* c = ctxs[d];
+        Shard& s = sh[d];
+        s.lo = n * d / n_ctx;
+        s.cnt = n * (d + 1) / n_ctx - s.lo;
+        TRY(use(c));
+        size_t cnt = s.cnt ? s.cnt : 1;
+        TRY(s.a.alloc(cnt * sizeof(G1))); TRY(s.b.alloc(cnt * sizeof(G2)));
+        TRY(s.f.alloc(cnt * sizeof(Fq12))); TRY(s.s.alloc(((cnt + 1) / 2) * sizeof(Fq12)));
+        if (s.cnt == 0) {   // empty shard contributes one
+            LAUNCH(c, (k_miller_product<1, 4>), 1, (const G1*)nullptr, (const G2*)nullptr, 0, (const G1*)nullptr,
+                   (const uint4*)nullptr, 0, s.f.as<Fq12>(), (size_t)1);
+            s.res = s.f.as<Fq12>();
+            continue;
+        }
+        TRY(h2d(c, s.a.p, (const uint8_t*)g1 + s.lo * sizeof(G1), s.cnt * sizeof(G1)));
+        TRY(h2d(c, s.b.p, (const uint8_t*)g2 + s.lo * sizeof(G2), s.cnt * sizeof(G2)));
+        LAUNCH(c, k_miller_many, s.cnt, s.b.as<G2>(), s.a.as<G1>(), s.f.as<Fq12>(), (uint8_t*)nullptr, s.cnt);
+        TRY(tree_product(c, s.f.as<Fq12>(), s.s.as<Fq12>(), s.cnt, &s.res));
+    }
+    // phase 2: gather the partials on device 0 (peer copy over NVLink; staged by the driver if no P2P)
+    for (size_t d = 0; d < n_ctx; d++) {
+        bn254_ctx* c = ctxs[d];
+        TRY(use(c));
+        CU(cudaMemcpyPeerAsync(partials.as<Fq12>() + d, c0->device, sh[d].res, c->device, sizeof(Fq12), c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+    }
+    // phase 3: <= n_ctx-1 Fq12 multiplications and ONE final exponentiation on device 0
+    TRY(use(c0));
+    Fq12* res = nullptr;
+    TRY(tree_product(c0, partials.as<Fq12>(), scratch.as<Fq12>(), n_ctx, &res));
+    LAUNCH(c0, k_final_exp_many, 1, (const Fq12*)res, out.as<Fq12>(), (uint8_t*)nullptr, flag.as<uint8_t>(), (size_t)1);
+    if (gt_out) TRY(d2h(c0, gt_out, out.p, sizeof(Fq12)));
+    if (is_one) TRY(d2h(c0, is_one, flag.p, 1));
+    CU(cudaStreamSynchronize(c0->stream));
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// field-level test hook and roofline microbenchmarks
+// ---------------------------------------------------------------------------------------------
+int bn254_field_op_many(bn254_ctx* ctx, int op, const void* a, const void* b, void* out, size_t n) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    static const size_t unit_of[10] = {32, 32, 32, 64, 64, 192, 384, 384, 384, 32};
+    if (op < 0 || op > 9 || !a || !out) return fail(BN254_ERR_ARG, "bad argument");
+    bool binary = (op == 0 || op == 1 || op == 2 || op == 3 || op == 5 || op == 6);
+    if (binary && !b) return fail(BN254_ERR_ARG, "null pointer");
+    size_t bytes = unit_of[op] * n;
+    DevBuf x, y, o;
+    TRY(x.alloc(bytes)); TRY(y.alloc(bytes)); TRY(o.alloc(bytes));
+    TRY(h2d(ctx, x.p, a, bytes));
+    if (binary) TRY(h2d(ctx, y.p, b, bytes));
+    LAUNCH(ctx, k_field_op, n, op, x.as<uint4>(), y.as<uint4>(), o.as<uint4>(), n);
+    TRY(d2h(ctx, out, o.p, bytes));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int bn254_microbench(bn254_ctx* ctx, int kind, int grid, int block, int iters, double* ms, double* ops) {
+    TRY(use(ctx));
+    if (kind < 0 || kind > 2 || grid <= 0 || block <= 0 || block > 256 || iters <= 0 || !ms || !ops) return fail(BN254_ERR_ARG, "bad argument");
+    DevBuf sink;
+    TRY(sink.alloc(16));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0)); CU(cudaEventCreate(&e1));
+    for (int rep = 0; rep < 2; rep++) {   // first pass warms up
+        CU(cudaEventRecord(e0, ctx->stream));
+        if (kind == 0) k_microbench<0><<<grid, block, 0, ctx->stream>>>(sink.as<uint32_t>(), iters, 12345u);
+        else if (kind == 1) k_microbench<1><<<grid, block, 0, ctx->stream>>>(sink.as<uint32_t>(), iters, 12345u);
+        else k_microbench<2><<<grid, block, 0, ctx->stream>>>(sink.as<uint32_t>(), iters, 12345u);
+        ctx->launches.fetch_add(1);
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(e1, ctx->stream));
+        CU(cudaEventSynchronize(e1));
+    }
+    float t = 0;
+    CU(cudaEventElapsedTime(&t, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    *ms = t;
+    double threads = (double)grid * block;
+    *ops = threads * iters * (kind == 2 ? 8.0 : 128.0);   // kinds 0/1: 16 x 8 mads per iteration; kind 2: 8 Fq muls
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,374 @@
+// CUDA kernels of the BN254 pairing engine (sm_100a).  One thread per unit of work (pairing,
+// product check, scalar multiplication); Fq12 state in per-thread local memory, Fq2-level bodies
+// register-blocked around the IMAD.WIDE carry chains of fq_ptx.cuh.  See DESIGN.md for the layout.
+#pragma once
+#include "bn_curve.cuh"
+
+namespace bn {
+
+#ifndef BN_BLOCK
+#define BN_BLOCK 64
+#endif
+#ifndef BN_MIN_BLOCKS
+#define BN_MIN_BLOCKS 4
+#endif
+#define BN_KERNEL __global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS)
+
+__device__ __forceinline__ size_t gtid() { return (size_t)blockIdx.x * blockDim.x + threadIdx.x; }
+
+// ---------------------------------------------------------------------------------------------
+// affine conversion of one (G1, G2) pair with ONE Fermat inversion (the reference does two,
+// src/groups/mod.rs:895; same field elements).  false if either point is at infinity.
+// ---------------------------------------------------------------------------------------------
+__device__ __noinline__ bool pair_to_affine(AffG1& pa, AffG2& qa, const G1& p, const G2& q) {
+    if (fq_is_zero(p.z) || fq2_is_zero(q.z)) return false;
+    Fq n, t, ti, pzi, ni, z2, z3;
+    fq_mul(n, q.z.c0, q.z.c0);
+    fq_mul(t, q.z.c1, q.z.c1);
+    fq_add(n, n, t);                 // norm(q.z) != 0
+    fq_mul_ni(t, p.z, n);
+    fq_inv(ti, t);
+    fq_mul_ni(pzi, ti, n);           // 1/p.z
+    fq_mul_ni(ni, ti, p.z);          // 1/norm
+    fq_mul_ni(z2, pzi, pzi);
+    fq_mul_ni(pa.x, p.x, z2);
+    fq_mul_ni(z3, z2, pzi);
+    fq_mul_ni(pa.y, p.y, z3);
+    Fq2 qzi, w2, w3;
+    fq_mul_ni(qzi.c0, q.z.c0, ni);
+    fq_mul_ni(t, q.z.c1, ni);
+    fq_neg(qzi.c1, t);               // 1/q.z = conj(q.z)/norm
+    fq2_sqr(w2, qzi);
+    fq2_mul(qa.x, q.x, w2);
+    fq2_mul(w3, w2, qzi);
+    fq2_mul(qa.y, q.y, w3);
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------
+// pairing = Miller kernel + final-exponentiation kernel (the 384-byte Miller value makes one trip
+// through HBM: negligible against ~4.7 M IMADs per pairing, and each phase gets its own register
+// allocation).  lib.rs:611-613 / groups/mod.rs:894-902.
+// ---------------------------------------------------------------------------------------------
+BN_KERNEL k_miller_many(const G2* __restrict__ q, const G1* __restrict__ p, Fq12* __restrict__ f_out,
+                        uint8_t* __restrict__ ok, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    G1 pp = p[i];
+    G2 qq = q[i];
+    AffG1 pa;
+    AffG2 qa;
+    Fq12 f = fq12_one();
+    bool good = pair_to_affine(pa, qa, pp, qq);
+    if (good) miller_loop_fused(f, pa, qa);
+    f_out[i] = f;
+    if (ok) ok[i] = good ? 1 : 0;
+}
+
+BN_KERNEL k_final_exp_many(const Fq12* __restrict__ in, Fq12* __restrict__ out, uint8_t* __restrict__ some,
+                           uint8_t* __restrict__ is_one, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Fq12 f = in[i], r;
+    bool s = fq12_final_exponentiation(r, f);
+    if (out) out[i] = r;
+    if (some) some[i] = s ? 1 : 0;
+    if (is_one) {
+        Fq12 one = fq12_one();
+        is_one[i] = fq12_eq(r, one) ? 1 : 0;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// product checks: one thread per check, shared squaring chain (groups::miller_loop_batch,
+// src/groups/mod.rs:609-640), line coefficients of the variable G2 points produced on the fly,
+// those of shared G2 points read from device tables (broadcast loads).
+// Table layout: uint4 tab[(c * 12 + w) * n_tables + j] = 16-byte word w of coefficient c of table j
+// (word-major SoA: coalesced when thread i reads table i, a broadcast when all read table j).
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void load_coeff(EllCoeffs& c, const uint4* __restrict__ tab, size_t n_tables, size_t j, int idx) {
+    uint4* dst = reinterpret_cast<uint4*>(&c);
+#pragma unroll
+    for (int w = 0; w < 12; w++) dst[w] = __ldg(&tab[((size_t)idx * 12 + w) * n_tables + j]);
+}
+
+template <int MAXV, int MAXS>
+BN_KERNEL k_miller_product(const G1* __restrict__ g1v, const G2* __restrict__ g2v, int v,
+                           const G1* __restrict__ g1s, const uint4* __restrict__ tab, int m,
+                           Fq12* __restrict__ f_out, size_t n_checks) {
+    size_t i = gtid();
+    if (i >= n_checks) return;
+    G2 R[MAXV];
+    AffG2 Q[MAXV];
+    AffG1 P[MAXV];
+    AffG1 PS[MAXS];
+    int js[MAXS];
+    int nv = 0, ns = 0;
+    for (int j = 0; j < v; j++) {       // skip semantics of pairing_batch, src/groups/mod.rs:909-920
+        G1 pp = g1v[i * v + j];
+        G2 qq = g2v[i * v + j];
+        if (pair_to_affine(P[nv], Q[nv], pp, qq)) {
+            R[nv].x = Q[nv].x; R[nv].y = Q[nv].y; R[nv].z = fq2_one();
+            nv++;
+        }
+    }
+    for (int j = 0; j < m; j++) {
+        G1 pp = g1s[i * m + j];
+        if (jac_to_affine(PS[ns], pp)) js[ns++] = j;
+    }
+    Fq12 f = fq12_one();
+    EllCoeffs c;
+    int idx = 0;
+    bool started = false;
+    for (int k = 0; k < 64; k++) {
+        if (started) fq12_sqr(f, f);
+        for (int j = 0; j < nv; j++) { g2_doubling_step(R[j], c); line_mul(f, c, P[j]); started = true; }
+        for (int j = 0; j < ns; j++) { load_coeff(c, tab, m, js[j], idx); line_mul(f, c, PS[j]); started = true; }
+        idx++;
+        uint32_t d = naf_digit(k);
+        if (d != 0) {
+            for (int j = 0; j < nv; j++) {
+                AffG2 qn = Q[j];
+                if (d == 3) fq2_neg(qn.y, qn.y);
+                g2_mixed_addition_step(R[j], qn, c);
+                line_mul(f, c, P[j]);
+            }
+            for (int j = 0; j < ns; j++) { load_coeff(c, tab, m, js[j], idx); line_mul(f, c, PS[j]); }
+            idx++;
+        }
+    }
+    for (int step = 0; step < 2; step++) {
+        for (int j = 0; j < nv; j++) {
+            AffG2 q1, q2;
+            g2_mul_by_q(q1, Q[j]);
+            if (step == 1) { g2_mul_by_q(q2, q1); fq2_neg(q2.y, q2.y); q1 = q2; }
+            g2_mixed_addition_step(R[j], q1, c);
+            line_mul(f, c, P[j]);
+        }
+        for (int j = 0; j < ns; j++) { load_coeff(c, tab, m, js[j], idx); line_mul(f, c, PS[j]); }
+        idx++;
+    }
+    f_out[i] = f;
+}
+
+// pair i against table i (materialised-G2Precomp streaming variant: coalesced table reads)
+BN_KERNEL k_miller_precomp_each(const G1* __restrict__ g1, const uint4* __restrict__ tab, size_t n_tables,
+                                Fq12* __restrict__ f_out, uint8_t* __restrict__ ok, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    G1 pp = g1[i];
+    AffG1 pa;
+    Fq12 f = fq12_one();
+    bool good = jac_to_affine(pa, pp);
+    if (good) {
+        EllCoeffs c;
+        int idx = 0;
+        for (int k = 0; k < 64; k++) {
+            if (k) fq12_sqr(f, f);
+            load_coeff(c, tab, n_tables, i, idx++); line_mul(f, c, pa);
+            if (naf_digit(k)) { load_coeff(c, tab, n_tables, i, idx++); line_mul(f, c, pa); }
+        }
+        load_coeff(c, tab, n_tables, i, idx++); line_mul(f, c, pa);
+        load_coeff(c, tab, n_tables, i, idx++); line_mul(f, c, pa);
+    }
+    f_out[i] = f;
+    if (ok) ok[i] = good ? 1 : 0;
+}
+
+// AffineG2::precompute for n points into the word-major table; bad[0] set if any point is at infinity
+struct TableSink {
+    uint4* tab; size_t n_tables, j; int idx;
+    __device__ __forceinline__ void put(const EllCoeffs& c) {
+        const uint4* src = reinterpret_cast<const uint4*>(&c);
+#pragma unroll
+        for (int w = 0; w < 12; w++) tab[((size_t)idx * 12 + w) * n_tables + j] = src[w];
+        idx++;
+    }
+    __device__ __forceinline__ void dbl(const EllCoeffs& c, int) { put(c); }
+    __device__ __forceinline__ void add(const EllCoeffs& c) { put(c); }
+};
+BN_KERNEL k_g2_precompute(const G2* __restrict__ q, uint4* __restrict__ tab, AffG2* __restrict__ q_aff,
+                          int* __restrict__ bad, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    G2 qq = q[i];
+    AffG2 qa;
+    if (!jac_to_affine(qa, qq)) { atomicExch(bad, 1); return; }
+    q_aff[i] = qa;
+    TableSink s;
+    s.tab = tab; s.n_tables = n; s.j = i; s.idx = 0;
+    g2_walk_lines(qa, s);
+}
+
+// out[g] = prod_{j < group} in[g*group + j]
+BN_KERNEL k_fq12_group_product(const Fq12* __restrict__ in, size_t group, Fq12* __restrict__ out, size_t n_groups) {
+    size_t g = gtid();
+    if (g >= n_groups) return;
+    Fq12 acc = in[g * group];
+    for (size_t j = 1; j < group; j++) { Fq12 b = in[g * group + j]; fq12_mul(acc, acc, b); }
+    out[g] = acc;
+}
+// one tree level: out[i] = in[2i] * in[2i+1] (last element copied when n is odd)
+BN_KERNEL k_fq12_pair_product(const Fq12* __restrict__ in, size_t n, Fq12* __restrict__ out) {
+    size_t i = gtid();
+    size_t n_out = (n + 1) / 2;
+    if (i >= n_out) return;
+    Fq12 a = in[2 * i];
+    if (2 * i + 1 < n) { Fq12 b = in[2 * i + 1]; fq12_mul(a, a, b); }
+    out[i] = a;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Gt algebra (src/lib.rs:584-609), scalar multiplication (src/lib.rs:425-431, :576-582), normalize
+// ---------------------------------------------------------------------------------------------
+BN_KERNEL k_gt_mul(const Fq12* __restrict__ a, const Fq12* __restrict__ b, Fq12* __restrict__ out, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Fq12 x = a[i], y = b[i];
+    fq12_mul(x, x, y);
+    out[i] = x;
+}
+BN_KERNEL k_gt_pow(const Fq12* __restrict__ a, const Fq* __restrict__ fr, Fq12* __restrict__ out, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Fq12 x = a[i], r;
+    Fq m = fr[i];
+    uint32_t k[8];
+    fr_to_canonical(k, m.v);
+    fq12_pow(r, x, k);
+    out[i] = r;
+}
+BN_KERNEL k_gt_inverse(const Fq12* __restrict__ a, Fq12* __restrict__ out, uint8_t* __restrict__ some, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Fq12 x = a[i], r;
+    bool s = fq12_inv(r, x);
+    out[i] = r;
+    if (some) some[i] = s ? 1 : 0;
+}
+__global__ void k_gt_eq(const Fq12* __restrict__ a, const Fq12* __restrict__ b, uint8_t* __restrict__ eq, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    const uint4* x = reinterpret_cast<const uint4*>(a + i);
+    const uint4* y = reinterpret_cast<const uint4*>(b + i);
+    uint32_t d = 0;
+#pragma unroll
+    for (int w = 0; w < 24; w++) {
+        uint4 u = x[w], v = y[w];
+        d |= (u.x ^ v.x) | (u.y ^ v.y) | (u.z ^ v.z) | (u.w ^ v.w);
+    }
+    eq[i] = d == 0;
+}
+template <class F>
+BN_KERNEL k_jac_mul(const Jac<F>* __restrict__ p, const Fq* __restrict__ fr, Jac<F>* __restrict__ out, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Jac<F> x = p[i], r;
+    Fq m = fr[i];
+    uint32_t k[8];
+    fr_to_canonical(k, m.v);
+    jac_mul(r, x, k);
+    out[i] = r;
+}
+template <class F>
+BN_KERNEL k_jac_normalize(const Jac<F>* __restrict__ p, Jac<F>* __restrict__ out, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Jac<F> x = p[i], r;
+    jac_normalize(r, x);
+    out[i] = r;
+}
+
+// field-level test hook (bn254_field_op_many)
+BN_KERNEL k_field_op(int op, const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ out, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    switch (op) {
+        case 0: case 1: case 2: case 9: {
+            Fq x = reinterpret_cast<const Fq*>(a)[i], r;
+            if (op == 9) { fq_inv(r, x); }
+            else {
+                Fq y = reinterpret_cast<const Fq*>(b)[i];
+                if (op == 0) fq_mul(r, x, y); else if (op == 1) fq_add(r, x, y); else fq_sub(r, x, y);
+            }
+            reinterpret_cast<Fq*>(out)[i] = r;
+        } break;
+        case 3: case 4: {
+            Fq2 x = reinterpret_cast<const Fq2*>(a)[i], r;
+            if (op == 3) { Fq2 y = reinterpret_cast<const Fq2*>(b)[i]; fq2_mul(r, x, y); } else fq2_sqr(r, x);
+            reinterpret_cast<Fq2*>(out)[i] = r;
+        } break;
+        case 5: {
+            Fq6 x = reinterpret_cast<const Fq6*>(a)[i], y = reinterpret_cast<const Fq6*>(b)[i], r;
+            fq6_mul(r, x, y);
+            reinterpret_cast<Fq6*>(out)[i] = r;
+        } break;
+        default: {
+            Fq12 x = reinterpret_cast<const Fq12*>(a)[i], r;
+            if (op == 6) { Fq12 y = reinterpret_cast<const Fq12*>(b)[i]; fq12_mul(r, x, y); }
+            else if (op == 7) fq12_sqr(r, x);
+            else fq12_cyclotomic_sqr(r, x);
+            reinterpret_cast<Fq12*>(out)[i] = r;
+        } break;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// roofline microbenchmarks: register-only chains.  kind 0: mad.lo.u32 (IMAD), 1: mad.wide.u32
+// (IMAD.WIDE), 2: dependent Fq Montgomery multiplications (2 independent streams per thread).
+// ---------------------------------------------------------------------------------------------
+template <int KIND>
+__global__ void __launch_bounds__(256) k_microbench(uint32_t* sink, int iters, uint32_t seed) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (KIND == 0) {
+        uint32_t x[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) x[j] = t * 2654435761u + j + seed;
+        uint32_t m = seed | 1u;
+        for (int it = 0; it < iters; it++) {
+#pragma unroll
+            for (int r = 0; r < 16; r++) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x[j]) : "r"(m), "r"(x[(j + 1) & 7]));
+            }
+        }
+        uint32_t s = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) s ^= x[j];
+        if (s == 0x12345678u) sink[0] = s;
+    } else if (KIND == 1) {
+        unsigned long long x[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) x[j] = ((unsigned long long)t << 20) + j + seed;
+        uint32_t m = seed | 1u;
+        for (int it = 0; it < iters; it++) {
+#pragma unroll
+            for (int r = 0; r < 16; r++) {
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    uint32_t lo = (uint32_t)x[j];
+                    asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(x[j]) : "r"(lo), "r"(m));
+                }
+            }
+        }
+        unsigned long long s = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) s ^= x[j];
+        if (s == 0x12345678ull) sink[0] = (uint32_t)s;
+    } else {
+        Fq a, b, c;
+#pragma unroll
+        for (int j = 0; j < 8; j++) { a.v[j] = t + j + seed; b.v[j] = t * 3 + j; c.v[j] = j + 1; }
+        a.v[7] &= 0x0fffffffu; b.v[7] &= 0x0fffffffu;
+        for (int it = 0; it < iters; it++) {
+#pragma unroll
+            for (int r = 0; r < 4; r++) { fq_mul(a, a, c); fq_mul(b, b, c); }
+        }
+        uint32_t s = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) s ^= a.v[j] ^ b.v[j];
+        if (s == 0x12345678u) sink[0] = s;
+    }
+}
+
+}  // namespace bn

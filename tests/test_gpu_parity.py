@@ -1,0 +1,271 @@
+"""Parity tests proper: the CUDA path, called through the C ABI (libbn254_b200.so via ctypes), against
+the C oracle on the same seeded inputs, against the reference's golden vectors, and -- at the full
+BASELINE.json sizes -- through size-independent properties.  Bit-exact everywhere (integer work)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import bn254_ref as o
+from oracle import c_oracle as c
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+G1, G2, GT, FR = 96, 192, 384, 32
+
+
+@pytest.fixture(scope="module")
+def eng():
+    import paritytech_bn_b200 as bn
+    e = bn.Engine(0)
+    yield e
+    e.close()
+
+
+def _b(x):
+    return np.frombuffer(o.to_bytes(x), dtype=np.uint8).copy()
+
+
+def _rand_fq_elems(rng, n_fq, n, edge=True):
+    vals = rng.integers(0, 2**63, size=(n * n_fq, 5), dtype=np.uint64)
+    out = []
+    for row in vals:
+        v = 0
+        for w in row:
+            v = (v << 63) | int(w)
+        out.append(v % o.Q)
+    if edge:
+        for k, v in enumerate([0, 1, o.Q - 1, o.Q - 2, 2, o.MONT_R % o.Q]):
+            if k < len(out):
+                out[k * max(1, len(out) // 7)] = v
+    return np.frombuffer(b"".join(o.fq_to_mont(v).to_bytes(32, "little") for v in out), dtype=np.uint8).copy()
+
+
+@pytest.mark.parametrize("name,unit,ref", [
+    ("fq_mul", 32, c.fq_mul), ("fq_add", 32, c.fq_add), ("fq_sub", 32, c.fq_sub),
+    ("fq2_mul", 64, c.fq2_mul), ("fq6_mul", 192, c.fq6_mul), ("fq12_mul", 384, c.fq12_mul),
+])
+def test_field_binary(eng, name, unit, ref):
+    rng = np.random.default_rng(1)
+    n = 4096 if unit <= 64 else 512
+    a, b = _rand_fq_elems(rng, unit // 32, n), _rand_fq_elems(rng, unit // 32, n)
+    assert eng.field_op(name, a, b).tobytes() == ref(a, b).tobytes()
+    assert eng.field_op(name, a, a).tobytes() == ref(a, a).tobytes()
+
+
+@pytest.mark.parametrize("name,unit,ref", [
+    ("fq2_sqr", 64, c.fq2_sqr), ("fq12_sqr", 384, c.fq12_sqr),
+])
+def test_field_unary(eng, name, unit, ref):
+    rng = np.random.default_rng(2)
+    a = _rand_fq_elems(rng, unit // 32, 512)
+    assert eng.field_op(name, a).tobytes() == ref(a).tobytes()
+
+
+def test_fq_inverse(eng):
+    rng = np.random.default_rng(3)
+    a = _rand_fq_elems(rng, 1, 256)
+    ro, some = c.fq_inv(a)
+    assert eng.field_op("fq_inv", a).tobytes() == ro.tobytes()     # zero -> zero
+
+
+def test_golden_reduced_pairing(eng, golden):
+    """src/groups/mod.rs:928-999 through the C ABI, incl. G*Fr and the pre-final-exp value (:642-691)."""
+    v = golden["test_reduced_pairing"]
+    k1 = util.fr_bytes([int(v["g1_scalar"])])
+    k2 = util.fr_bytes([int(v["g2_scalar"])])
+    p = eng.g1_mul(util.G1_GEN, k1)
+    q = eng.g2_mul(util.G2_GEN, k2)
+    assert p.tobytes() == c.g1_mul(util.G1_GEN, k1).tobytes()
+    assert q.tobytes() == c.g2_mul(util.G2_GEN, k2).tobytes()
+    gt = eng.pairing(p, q)
+    assert gt.tobytes() == util.fq_mont_bytes([int(x) for x in v["expected"]])
+    m = golden["test_miller_loop"]
+    ml = eng.miller_loop_batch(q, p)
+    assert ml.tobytes() == util.fq_mont_bytes([int(x) for x in m["expected"]])
+    fe, some = eng.final_exponentiation(ml)
+    assert some[0] == 1 and fe.tobytes() == gt.tobytes()
+
+
+def test_golden_prepared_g2(eng, golden):
+    """All 87 EllCoeffs of src/groups/mod.rs:779-892 from the device table."""
+    v = golden["test_prepared_g2"]
+    q = eng.g2_mul(util.G2_GEN, util.fr_bytes([int(v["g2_scalar"])]))
+    pc = eng.g2_precompute(np.concatenate([q, util.G2_GEN]))
+    assert len(pc) == 2
+    exp = util.fq_mont_bytes([int(x) for x in v["q"]["x"] + v["q"]["y"]])
+    for e in v["coeffs"]:
+        exp += util.fq_mont_bytes([int(x) for x in e["ell_0"] + e["ell_vw"] + e["ell_vv"]])
+    assert pc.export(0).tobytes() == exp
+    assert pc.export(1).tobytes() == c.g2_precompute(util.G2_GEN).tobytes()
+    pc.close()
+
+
+def _workload(n, stream):
+    ks1 = util.scalars(n, stream=stream)
+    ks2 = util.scalars(n, stream=stream + 100)
+    return util.points_cpu(ks1, ks2)
+
+
+def test_pairing_many_vs_oracle(eng):
+    n = int(os.environ.get("BN_TEST_PAIRINGS", "2048"))
+    g1, g2 = _workload(n, 1)
+    g1 = g1.reshape(n, G1).copy()
+    g2 = g2.reshape(n, G2).copy()
+    # injected edge cases: infinity on either side, generators with z == 1, a = r-1
+    g1[3], g2[5] = util.G1_INF, util.G2_INF
+    g1[7], g2[7] = util.G1_INF, util.G2_INF
+    g1[9], g2[9] = util.G1_GEN, util.G2_GEN
+    g1[11] = c.g1_mul(util.G1_GEN, util.fr_bytes([o.R_ORDER - 1]))
+    g1, g2 = g1.reshape(-1), g2.reshape(-1)
+    got = eng.pairing(g1, g2)
+    exp = c.pairing_many(g1, g2)
+    assert got.tobytes() == exp.tobytes()
+    assert got.reshape(n, GT)[3].tobytes() == util.GT_ONE.tobytes()
+    # canonical (non-Montgomery big-endian) serialisation agrees too
+    can = c.fq_to_canonical(got[:GT])
+    assert can.tobytes() == c.fq_to_canonical(exp[:GT]).tobytes()
+    # the split public API: miller_loop_many + final_exponentiation
+    ml, ok = eng.miller_loop_many(g2, g1)
+    rml, rok = c.miller_loop_many(g2, g1)
+    assert (ok == rok).all() and ml.tobytes() == rml.tobytes()
+    fe, some = eng.final_exponentiation(ml)
+    assert some.all() and fe.tobytes() == exp.tobytes()
+
+
+def test_pairing_batch_checks_vs_oracle(eng):
+    n_checks = 256
+    w = util.groth16_checks(n_checks)
+    out, is_one = eng.pairing_batch(w["g1"], w["g2"], pairs_per_check=4)
+    rout, ris = c.pairing_product_many(w["g1"], w["g2"], 4)
+    assert (is_one == w["valid"]).all() and (ris == is_one).all()
+    assert out.tobytes() == rout.tobytes()
+    # same checks through the shared-G2Precomp entry point
+    pc = eng.g2_precompute(w["vk_g2"])
+    out2, is_one2 = eng.pairing_batch_precomp(pc, w["g1_shared"], w["g1_var"], w["g2_var"], 1)
+    assert out2.tobytes() == rout.tobytes() and (is_one2 == is_one).all()
+    pc.close()
+
+
+def test_pairing_batch_edge_semantics(eng):
+    g1, g2 = _workload(6, 3)
+    g1 = g1.reshape(6, G1).copy()
+    g2 = g2.reshape(6, G2).copy()
+    g1[1] = util.G1_INF          # skipped pair
+    g2[2] = util.G2_INF          # skipped pair
+    g1, g2 = g1.reshape(-1), g2.reshape(-1)
+    out, _ = eng.pairing_batch(g1, g2)                      # one product of 6 pairs
+    assert out.tobytes() == c.pairing_batch(g1, g2).tobytes()
+    out3, _ = eng.pairing_batch(g1, g2, pairs_per_check=3)  # two checks of 3
+    assert out3.tobytes() == c.pairing_product_many(g1, g2, 3)[0].tobytes()
+    out2, _ = eng.pairing_batch(g1, g2, pairs_per_check=2)
+    assert out2.tobytes() == c.pairing_product_many(g1, g2, 2)[0].tobytes()
+    # all pairs skipped -> one
+    out, is_one = eng.pairing_batch(np.tile(util.G1_INF, 2), g2[:2 * G2])
+    assert out.tobytes() == util.GT_ONE.tobytes() and is_one[0] == 1
+    # more pairs per check than the fused kernel handles (falls to per-pair Miller + product)
+    g1b, g2b = _workload(24, 4)
+    outb, _ = eng.pairing_batch(g1b, g2b, pairs_per_check=12)
+    assert outb.tobytes() == c.pairing_product_many(g1b, g2b, 12)[0].tobytes()
+
+
+def test_miller_loop_batch_api(eng):
+    import paritytech_bn_b200 as bn
+    g1, g2 = _workload(5, 5)
+    assert eng.miller_loop_batch(g2, g1).tobytes() == c.miller_loop_batch(g2, g1).tobytes()
+    assert eng.miller_loop_batch(g2[:G2], g1[:G1]).tobytes() == c.miller_loop_batch(g2[:G2], g1[:G1]).tobytes()
+    assert eng.miller_loop_batch(np.zeros(0, np.uint8), np.zeros(0, np.uint8)).tobytes() == util.GT_ONE.tobytes()
+    bad = g2.copy()
+    bad[G2:2 * G2] = util.G2_INF
+    with pytest.raises(bn.CurveError):
+        eng.miller_loop_batch(bad, g1)
+
+
+def test_scalar_mul_vs_oracle(eng):
+    n = 1024
+    ks = util.scalars(n, stream=11)
+    base1, base2 = _workload(n, 12)
+    sc = [0, 1, 2, o.R_ORDER - 1] + ks[4:]
+    fr = util.fr_bytes(sc)
+    got1 = eng.g1_mul(base1, fr)
+    assert got1.tobytes() == c.g1_mul(base1, fr).tobytes()          # raw Jacobian equality
+    n2 = 256
+    got2 = eng.g2_mul(base2[:n2 * G2], fr[:n2 * FR])
+    assert got2.tobytes() == c.g2_mul(base2[:n2 * G2], fr[:n2 * FR]).tobytes()
+    assert eng.g1_normalize(got1).tobytes() == c.g1_normalize(got1).tobytes()
+    assert eng.g2_normalize(got2).tobytes() == c.g2_normalize(got2).tobytes()
+    inf = np.concatenate([util.G1_INF, util.G1_GEN])
+    assert eng.g1_normalize(inf).tobytes() == inf.tobytes()
+
+
+def test_gt_algebra_and_joux(eng):
+    """Gt::{mul,pow,inverse,==} and the Joux three-party check of examples/joux.rs:7-21."""
+    a, b, cc = util.scalars(3, stream=21)
+    fa, fb, fc = util.fr_bytes([a]), util.fr_bytes([b]), util.fr_bytes([cc])
+    pa, pb, pc_ = (eng.g1_mul(util.G1_GEN, f) for f in (fa, fb, fc))
+    qa, qb, qc = (eng.g2_mul(util.G2_GEN, f) for f in (fa, fb, fc))
+    e = eng.pairing(np.concatenate([pb, pc_, pa]), np.concatenate([qc, qa, qb]))
+    shared = eng.gt_pow(e, np.concatenate([fa, fb, fc]))
+    k = shared.reshape(3, GT)
+    assert k[0].tobytes() == k[1].tobytes() == k[2].tobytes()
+    assert shared.tobytes() == c.gt_pow(e, np.concatenate([fa, fb, fc])).tobytes()
+    assert eng.gt_eq(shared, np.tile(k[0], 3)).all()
+    assert not eng.gt_eq(e, np.tile(k[0], 3)).any()
+    inv, some = eng.gt_inverse(e)
+    rinv, rsome = c.fq12_inverse(e)
+    assert some.all() and inv.tobytes() == rinv.tobytes()
+    assert eng.gt_mul(e, inv).tobytes() == np.tile(util.GT_ONE, 3).tobytes()
+    z, some = eng.gt_inverse(np.zeros(GT, np.uint8))
+    assert some[0] == 0
+    fe, some = eng.final_exponentiation(np.zeros(GT, np.uint8))       # Option::None
+    assert some[0] == 0
+
+
+def test_full_size_products_known_answer(eng):
+    """2^16 Groth16-shaped checks (BASELINE config #3 size) through a size-independent property:
+    valid checks are exactly one, tampered ones are not; inputs made by the CUDA scalar-mul kernels."""
+    n_checks = int(os.environ.get("BN_TEST_FULL_CHECKS", str(1 << 14)))
+
+    def smul(which, ks):
+        fr = util.fr_bytes(ks)
+        if which == "g1":
+            return eng.g1_mul(np.tile(util.G1_GEN, len(ks)), fr)
+        return eng.g2_mul(np.tile(util.G2_GEN, len(ks)), fr)
+
+    w = util.groth16_checks(n_checks, stream=31, scalar_mul=smul)
+    out, is_one = eng.pairing_batch(w["g1"], w["g2"], pairs_per_check=4)
+    assert (is_one == w["valid"]).all()
+    ones = out.reshape(n_checks, GT)[w["valid"] == 1]
+    assert (ones == util.GT_ONE).all()
+    # spot-check 64 of them bit-for-bit against the oracle
+    idx = np.arange(0, n_checks, max(1, n_checks // 64))[:64]
+    g1s = w["g1"].reshape(n_checks, 4 * G1)[idx].reshape(-1)
+    g2s = w["g2"].reshape(n_checks, 4 * G2)[idx].reshape(-1)
+    assert out.reshape(n_checks, GT)[idx].tobytes() == c.pairing_product_many(g1s, g2s, 4)[0].tobytes()
+
+
+def test_sharded_product(eng):
+    """One product split over contexts with the 384-byte partial gather (all on one GPU if only one)."""
+    import ctypes
+
+    import paritytech_bn_b200 as bn
+    n = 64
+    ks1 = util.scalars(n, stream=41)
+    ks2 = util.scalars(n, stream=42)
+    # sum a_i*b_i == 0 mod r  =>  the product is exactly one (SURVEY 8e known-answer construction)
+    tot = sum(x * y for x, y in zip(ks1[:-1], ks2[:-1])) % o.R_ORDER
+    ks1[-1] = (-tot * pow(ks2[-1], -1, o.R_ORDER)) % o.R_ORDER
+    g1, g2 = util.points_cpu(ks1, ks2)
+    import torch
+    ndev = min(torch.cuda.device_count(), 4)
+    engines = [eng] + [bn.Engine(d) for d in range(1, ndev)]
+    if ndev == 1:
+        engines.append(bn.Engine(0))      # two contexts on one device still exercise the gather path
+    out, is_one = bn.pairing_product_sharded(engines, g1, g2)
+    assert is_one and out.tobytes() == util.GT_ONE.tobytes()
+    g1[:G1] = util.G1_GEN
+    out, is_one = bn.pairing_product_sharded(engines, g1, g2)
+    assert not is_one and out.tobytes() == c.pairing_batch(g1, g2).tobytes()
+    for e in engines[1:]:
+        e.close()
