@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch-log2", type=int, default=16, help="pairings per GPU per step = 2^k")
-    ap.add_argument("--variant", default=None, help="library variant suffix ('' or '_r128')")
+    ap.add_argument("--variant", default=None, help="library variant suffix ('' or '_r255')")
     ap.add_argument("--cpu-sample", type=int, default=4096, help="pairings in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--extra", action="store_true", help="also time Groth16 checks and scalar muls (extra keys)")

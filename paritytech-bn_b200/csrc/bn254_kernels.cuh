@@ -10,7 +10,7 @@ namespace bn {
 #define BN_BLOCK 64
 #endif
 #ifndef BN_MIN_BLOCKS
-#define BN_MIN_BLOCKS 4
+#define BN_MIN_BLOCKS 8
 #endif
 #define BN_KERNEL __global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS)
 
