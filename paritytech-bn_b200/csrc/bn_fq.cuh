@@ -66,6 +66,29 @@ BN_HD void fq_set_zero(Fq& a) {
     for (int i = 0; i < 8; i++) a.v[i] = 0;
 }
 
+// 128-bit loads/stores of field elements that live in memory (local-memory Fq12 state, global I/O):
+// the out-of-line Fq2-level bodies read their operands with 2 x LD.128 per Fq instead of 8 scalar loads.
+BN_HD Fq fq_ld(const Fq& p) {
+#if defined(__CUDA_ARCH__)
+    const uint4* q = reinterpret_cast<const uint4*>(&p);
+    uint4 a = q[0], b = q[1];
+    Fq r;
+    r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; r.v[4] = b.x; r.v[5] = b.y; r.v[6] = b.z; r.v[7] = b.w;
+    return r;
+#else
+    return p;
+#endif
+}
+BN_HD void fq_st(Fq& p, const Fq& v) {
+#if defined(__CUDA_ARCH__)
+    uint4* q = reinterpret_cast<uint4*>(&p);
+    q[0] = make_uint4(v.v[0], v.v[1], v.v[2], v.v[3]);
+    q[1] = make_uint4(v.v[4], v.v[5], v.v[6], v.v[7]);
+#else
+    p = v;
+#endif
+}
+
 #if !defined(__CUDA_ARCH__)
 // ---------------------------------------------------------------------------------------------
 // host back end (test-only simulation of the device arithmetic)

@@ -33,7 +33,7 @@ BN_HD Fq fq_zero() { Fq r; fq_set_zero(r); return r; }
 // ---------------------------------------------------------------------------------------------
 // Fq helpers: Fermat inversion (replaces the divergent binary EEA of src/arith.rs:324-370)
 // ---------------------------------------------------------------------------------------------
-BN_HD_NOINLINE void fq_mul_ni(Fq& r, const Fq& a, const Fq& b) { fq_mul(r, a, b); }
+BN_HD_NOINLINE void fq_mul_ni(Fq& r, const Fq& a, const Fq& b) { Fq x = fq_ld(a), y = fq_ld(b), z; fq_mul(z, x, y); fq_st(r, z); }
 
 // r = a^(q-2); returns false (and r = 0) for a == 0, like Fq::inverse -> None (src/fields/fp.rs:108-117)
 BN_HD_NOINLINE bool fq_inv(Fq& r, const Fq& a) {
@@ -55,10 +55,20 @@ BN_HD Fq2 fq2_zero() { Fq2 r; fq_set_zero(r.c0); fq_set_zero(r.c1); return r; }
 BN_HD Fq2 fq2_one() { Fq2 r; r.c0 = fq_one(); fq_set_zero(r.c1); return r; }
 BN_HD bool fq2_is_zero(const Fq2& a) { return fq_is_zero(a.c0) && fq_is_zero(a.c1); }
 BN_HD bool fq2_eq(const Fq2& a, const Fq2& b) { return fq_eq(a.c0, b.c0) && fq_eq(a.c1, b.c1); }
-BN_ADD_FN void fq2_add(Fq2& r, const Fq2& a, const Fq2& b) { fq_add(r.c0, a.c0, b.c0); fq_add(r.c1, a.c1, b.c1); }
-BN_ADD_FN void fq2_sub(Fq2& r, const Fq2& a, const Fq2& b) { fq_sub(r.c0, a.c0, b.c0); fq_sub(r.c1, a.c1, b.c1); }
-BN_ADD_FN void fq2_neg(Fq2& r, const Fq2& a) { fq_neg(r.c0, a.c0); fq_neg(r.c1, a.c1); }
-BN_ADD_FN void fq2_dbl(Fq2& r, const Fq2& a) { fq_dbl(r.c0, a.c0); fq_dbl(r.c1, a.c1); }
+BN_HD Fq2 fq2_ld(const Fq2& p) { Fq2 r; r.c0 = fq_ld(p.c0); r.c1 = fq_ld(p.c1); return r; }
+BN_HD void fq2_st(Fq2& p, const Fq2& v) { fq_st(p.c0, v.c0); fq_st(p.c1, v.c1); }
+BN_ADD_FN void fq2_add(Fq2& r, const Fq2& a, const Fq2& b) {
+    Fq2 x = fq2_ld(a), y = fq2_ld(b), z;
+    fq_add(z.c0, x.c0, y.c0); fq_add(z.c1, x.c1, y.c1);
+    fq2_st(r, z);
+}
+BN_ADD_FN void fq2_sub(Fq2& r, const Fq2& a, const Fq2& b) {
+    Fq2 x = fq2_ld(a), y = fq2_ld(b), z;
+    fq_sub(z.c0, x.c0, y.c0); fq_sub(z.c1, x.c1, y.c1);
+    fq2_st(r, z);
+}
+BN_ADD_FN void fq2_neg(Fq2& r, const Fq2& a) { Fq2 x = fq2_ld(a), z; fq_neg(z.c0, x.c0); fq_neg(z.c1, x.c1); fq2_st(r, z); }
+BN_ADD_FN void fq2_dbl(Fq2& r, const Fq2& a) { Fq2 x = fq2_ld(a), z; fq_dbl(z.c0, x.c0); fq_dbl(z.c1, x.c1); fq2_st(r, z); }
 BN_HD void fq2_conj(Fq2& r, const Fq2& a) { r.c0 = a.c0; fq_neg(r.c1, a.c1); }   // frobenius_map(odd), fq2.rs:59-68
 
 // Karatsuba with lazy reduction; value of src/fields/fq2.rs:133-149
@@ -76,7 +86,7 @@ BN_HD void fq2_mul_inl(Fq2& r, const Fq2& a, const Fq2& b) {
     fq_redc(r.c0, t0);
     fq_redc(r.c1, s);
 }
-BN_HD_NOINLINE void fq2_mul(Fq2& r, const Fq2& a, const Fq2& b) { fq2_mul_inl(r, a, b); }
+BN_HD_NOINLINE void fq2_mul(Fq2& r, const Fq2& a, const Fq2& b) { Fq2 x = fq2_ld(a), y = fq2_ld(b), z; fq2_mul_inl(z, x, y); fq2_st(r, z); }
 
 // complex squaring; value of src/fields/fq2.rs:105-117
 BN_HD void fq2_sqr_inl(Fq2& r, const Fq2& a) {
@@ -87,21 +97,24 @@ BN_HD void fq2_sqr_inl(Fq2& r, const Fq2& a) {
     fq_mul(r.c0, s, d);
     fq_dbl(r.c1, m);
 }
-BN_HD_NOINLINE void fq2_sqr(Fq2& r, const Fq2& a) { fq2_sqr_inl(r, a); }
+BN_HD_NOINLINE void fq2_sqr(Fq2& r, const Fq2& a) { Fq2 x = fq2_ld(a), z; fq2_sqr_inl(z, x); fq2_st(r, z); }
 
 BN_HD_NOINLINE void fq2_scale(Fq2& r, const Fq2& a, const Fq& k) {   // src/fields/fq2.rs:48-53
-    fq_mul(r.c0, a.c0, k);
-    fq_mul(r.c1, a.c1, k);
+    Fq2 x = fq2_ld(a), z;
+    Fq kk = fq_ld(k);
+    fq_mul(z.c0, x.c0, kk);
+    fq_mul(z.c1, x.c1, kk);
+    fq2_st(r, z);
 }
 // a * (9 + u) = (9 a0 - a1) + (9 a1 + a0) u; value of src/fields/fq2.rs:55-57
-BN_ADD_FN void fq2_mul_by_xi(Fq2& r, const Fq2& a) {
-    Fq t0, t1, n0, n1;
+BN_ADD_FN void fq2_mul_by_xi(Fq2& r, const Fq2& aa) {
+    Fq2 a = fq2_ld(aa), n;
+    Fq t0, t1;
     fq_dbl(t0, a.c0); fq_dbl(t0, t0); fq_dbl(t0, t0); fq_add(t0, t0, a.c0);   // 9 a0
     fq_dbl(t1, a.c1); fq_dbl(t1, t1); fq_dbl(t1, t1); fq_add(t1, t1, a.c1);   // 9 a1
-    fq_sub(n0, t0, a.c1);
-    fq_add(n1, t1, a.c0);
-    r.c0 = n0;
-    r.c1 = n1;
+    fq_sub(n.c0, t0, a.c1);
+    fq_add(n.c1, t1, a.c0);
+    fq2_st(r, n);
 }
 BN_HD_NOINLINE bool fq2_inv(Fq2& r, const Fq2& a) {   // src/fields/fq2.rs:119-130
     Fq n, t, t2;
