@@ -163,7 +163,8 @@ BN_HD void fr_to_canonical(uint32_t (&out)[8], const uint32_t (&m)[8]) {
 struct EllCoeffs { Fq2 ell_0, ell_vw, ell_vv; };   // field order of src/groups/mod.rs:566-571
 
 // a/2 on the Montgomery image: (a + (a odd ? q : 0)) >> 1.  Same value as a * two_inv (:520-528).
-BN_HD void fq_half(Fq& r, const Fq& a) {
+BN_HD void fq_half(Fq& rr, const Fq& aa) {
+    Fq a = fq_ld(aa), r;
     uint32_t mask = 0u - (a.v[0] & 1u);
     uint32_t t[9];
     uint64_t c = 0;
@@ -174,6 +175,7 @@ BN_HD void fq_half(Fq& r, const Fq& a) {
     }
     t[8] = (uint32_t)c;
     for (int i = 0; i < 8; i++) r.v[i] = (t[i] >> 1) | (t[i + 1] << 31);
+    fq_st(rr, r);
 }
 BN_HD void fq2_half(Fq2& r, const Fq2& a) { fq_half(r.c0, a.c0); fq_half(r.c1, a.c1); }
 
@@ -214,7 +216,7 @@ BN_HD_NOINLINE void g2_mixed_addition_step(G2& r, const AffG2& base, EllCoeffs& 
     fq2_mul(t, e, base.x); fq2_mul(u, d, base.y); fq2_sub(t, t, u);
     fq2_mul_by_xi(out.ell_0, t);
     fq2_neg(out.ell_vv, e);
-    out.ell_vw = d;
+    cpv(out.ell_vw, d);
 }
 // AffineG2::mul_by_q, src/groups/mod.rs:694-699
 BN_HD void g2_mul_by_q(AffG2& r, const AffG2& q) {

@@ -57,6 +57,20 @@ BN_HD bool fq2_is_zero(const Fq2& a) { return fq_is_zero(a.c0) && fq_is_zero(a.c
 BN_HD bool fq2_eq(const Fq2& a, const Fq2& b) { return fq_eq(a.c0, b.c0) && fq_eq(a.c1, b.c1); }
 BN_HD Fq2 fq2_ld(const Fq2& p) { Fq2 r; r.c0 = fq_ld(p.c0); r.c1 = fq_ld(p.c1); return r; }
 BN_HD void fq2_st(Fq2& p, const Fq2& v) { fq_st(p.c0, v.c0); fq_st(p.c1, v.c1); }
+// memory-to-memory copies of tower elements with 128-bit accesses (alias-safe for d == s)
+template <class T> BN_HD void cpv(T& d, const T& s) {
+#if defined(__CUDA_ARCH__)
+    const uint4* sp = reinterpret_cast<const uint4*>(&s);
+    uint4* dp = reinterpret_cast<uint4*>(&d);
+    uint4 t[sizeof(T) / 16];
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); i++) t[i] = sp[i];
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(T) / 16); i++) dp[i] = t[i];
+#else
+    d = s;
+#endif
+}
 BN_ADD_FN void fq2_add(Fq2& r, const Fq2& a, const Fq2& b) {
     Fq2 x = fq2_ld(a), y = fq2_ld(b), z;
     fq_add(z.c0, x.c0, y.c0); fq_add(z.c1, x.c1, y.c1);
@@ -69,7 +83,7 @@ BN_ADD_FN void fq2_sub(Fq2& r, const Fq2& a, const Fq2& b) {
 }
 BN_ADD_FN void fq2_neg(Fq2& r, const Fq2& a) { Fq2 x = fq2_ld(a), z; fq_neg(z.c0, x.c0); fq_neg(z.c1, x.c1); fq2_st(r, z); }
 BN_ADD_FN void fq2_dbl(Fq2& r, const Fq2& a) { Fq2 x = fq2_ld(a), z; fq_dbl(z.c0, x.c0); fq_dbl(z.c1, x.c1); fq2_st(r, z); }
-BN_HD void fq2_conj(Fq2& r, const Fq2& a) { r.c0 = a.c0; fq_neg(r.c1, a.c1); }   // frobenius_map(odd), fq2.rs:59-68
+BN_HD void fq2_conj(Fq2& r, const Fq2& a) { Fq2 x = fq2_ld(a); fq_neg(x.c1, x.c1); fq2_st(r, x); }   // frobenius_map(odd), fq2.rs:59-68
 
 // Karatsuba with lazy reduction; value of src/fields/fq2.rs:133-149
 BN_HD void fq2_mul_inl(Fq2& r, const Fq2& a, const Fq2& b) {
@@ -141,9 +155,9 @@ BN_HD bool fq6_is_zero(const Fq6& a) { return fq2_is_zero(a.c0) && fq2_is_zero(a
 BN_HD void fq6_mul_by_v(Fq6& r, const Fq6& a) {   // mul_by_nonresidue, src/fields/fq6.rs:109-115
     Fq2 t;
     fq2_mul_by_xi(t, a.c2);
-    r.c2 = a.c1;
-    r.c1 = a.c0;
-    r.c0 = t;
+    cpv(r.c2, a.c1);
+    cpv(r.c1, a.c0);
+    cpv(r.c0, t);
 }
 BN_HD_NOINLINE void fq6_mul(Fq6& r, const Fq6& a, const Fq6& b) {   // value of src/fields/fq6.rs:194-208
     Fq2 aa, bb, cc, t, u, s;
@@ -157,7 +171,7 @@ BN_HD_NOINLINE void fq6_mul(Fq6& r, const Fq6& a, const Fq6& b) {   // value of 
     fq2_sub(s, s, aa); fq2_sub(s, s, bb); fq2_mul_by_xi(t, cc); fq2_add(n1, s, t);
     fq2_add(t, a.c0, a.c2); fq2_add(u, b.c0, b.c2); fq2_mul(s, t, u);
     fq2_sub(s, s, aa); fq2_add(s, s, bb); fq2_sub(n2, s, cc);
-    r.c0 = n0; r.c1 = n1; r.c2 = n2;
+    cpv(r.c0, n0); cpv(r.c1, n1); cpv(r.c2, n2);
 }
 BN_HD_NOINLINE void fq6_sqr(Fq6& r, const Fq6& a) {   // value of src/fields/fq6.rs:163-177
     Fq2 s0, s1, s2, s3, s4, t;
@@ -170,7 +184,7 @@ BN_HD_NOINLINE void fq6_sqr(Fq6& r, const Fq6& a) {   // value of src/fields/fq6
     fq2_mul_by_xi(t, s3); fq2_add(n0, s0, t);
     fq2_mul_by_xi(t, s4); fq2_add(n1, s1, t);
     fq2_add(n2, s1, s2); fq2_add(n2, n2, s3); fq2_sub(n2, n2, s0); fq2_sub(n2, n2, s4);
-    r.c0 = n0; r.c1 = n1; r.c2 = n2;
+    cpv(r.c0, n0); cpv(r.c1, n1); cpv(r.c2, n2);
 }
 BN_HD_NOINLINE void fq6_scale(Fq6& r, const Fq6& a, const Fq2& k) {   // src/fields/fq6.rs:117-123
     fq2_mul(r.c0, a.c0, k); fq2_mul(r.c1, a.c1, k); fq2_mul(r.c2, a.c2, k);
@@ -190,9 +204,10 @@ BN_HD_NOINLINE bool fq6_inv(Fq6& r, const Fq6& a) {   // src/fields/fq6.rs:179-1
 BN_HD void fq6_frobenius(Fq6& r, const Fq6& a, int power) {
     const Fq2 c1tab[3] = {BN_C_FROB6_C1_1, BN_C_FROB6_C1_2, BN_C_FROB6_C1_3};
     const Fq2 c2tab[3] = {BN_C_FROB6_C2_1, BN_C_FROB6_C2_2, BN_C_FROB6_C2_3};
-    Fq2 x0 = a.c0, x1 = a.c1, x2 = a.c2;
-    if (power & 1) { fq2_conj(x0, x0); fq2_conj(x1, x1); fq2_conj(x2, x2); }
-    r.c0 = x0;
+    Fq2 x0, x1, x2;
+    if (power & 1) { fq2_conj(x0, a.c0); fq2_conj(x1, a.c1); fq2_conj(x2, a.c2); }
+    else { cpv(x0, a.c0); cpv(x1, a.c1); cpv(x2, a.c2); }
+    cpv(r.c0, x0);
     fq2_mul(r.c1, x1, c1tab[power - 1]);
     fq2_mul(r.c2, x2, c2tab[power - 1]);
 }
@@ -233,7 +248,7 @@ BN_HD_NOINLINE void fq12_sqr(Fq12& r, const Fq12& a) {   // value of src/fields/
     fq6_sub(r.c0, s, t);
     fq6_dbl(r.c1, ab);
 }
-BN_HD void fq12_conj(Fq12& r, const Fq12& a) { r.c0 = a.c0; fq6_neg(r.c1, a.c1); }   // unitary_inverse, fq12.rs:126-128
+BN_HD void fq12_conj(Fq12& r, const Fq12& a) { if (&r != &a) cpv(r.c0, a.c0); fq6_neg(r.c1, a.c1); }   // unitary_inverse, fq12.rs:126-128
 BN_HD_NOINLINE bool fq12_inv(Fq12& r, const Fq12& a) {   // src/fields/fq12.rs:305-313
     Fq6 t, u;
     fq6_sqr(t, a.c0);
@@ -257,7 +272,8 @@ BN_HD_NOINLINE void fq12_frobenius(Fq12& r, const Fq12& a, int power) {   // src
 // f * (ell_0 + ell_vv v + ell_vw v w): sparse multiply; value of src/fields/fq12.rs:130-196.
 // x0 = ell_0, x2 = ell_vv, x4 = ell_vw (already scaled by P.x / P.y by the caller).
 BN_HD_NOINLINE void fq12_mul_by_024(Fq12& f, const Fq2& x0, const Fq2& x4, const Fq2& x2) {
-    Fq2 z0 = f.c0.c0, z1 = f.c0.c1, z2 = f.c0.c2, z3 = f.c1.c0, z4 = f.c1.c1, z5 = f.c1.c2;
+    Fq2 z0, z1, z2, z3, z4, z5;
+    cpv(z0, f.c0.c0); cpv(z1, f.c0.c1); cpv(z2, f.c0.c2); cpv(z3, f.c1.c0); cpv(z4, f.c1.c1); cpv(z5, f.c1.c2);
     Fq2 d0, d2, d4, s0, s1, t0, t1, t2, t3, t4;
     fq2_mul(d0, z0, x0);
     fq2_mul(d2, z2, x2);
@@ -318,7 +334,8 @@ BN_HD void fq4_sqr(Fq2& r0, Fq2& r1, const Fq2& a, const Fq2& b) {
     fq2_dbl(r1, tmp);
 }
 BN_HD_NOINLINE void fq12_cyclotomic_sqr(Fq12& r, const Fq12& a) {
-    Fq2 z0 = a.c0.c0, z4 = a.c0.c1, z3 = a.c0.c2, z2 = a.c1.c0, z1 = a.c1.c1, z5 = a.c1.c2;
+    Fq2 z0, z1, z2, z3, z4, z5;
+    cpv(z0, a.c0.c0); cpv(z4, a.c0.c1); cpv(z3, a.c0.c2); cpv(z2, a.c1.c0); cpv(z1, a.c1.c1); cpv(z5, a.c1.c2);
     Fq2 t0, t1, t2, t3, t4, t5, tmp;
     fq4_sqr(t0, t1, z0, z1);
     fq4_sqr(t2, t3, z2, z3);
@@ -330,14 +347,15 @@ BN_HD_NOINLINE void fq12_cyclotomic_sqr(Fq12& r, const Fq12& a) {
     fq2_sub(z3, t4, z3); fq2_dbl(z3, z3); fq2_add(z3, z3, t4);
     fq2_sub(z4, t2, z4); fq2_dbl(z4, z4); fq2_add(z4, z4, t2);
     fq2_add(z5, t3, z5); fq2_dbl(z5, z5); fq2_add(z5, z5, t3);
-    r.c0.c0 = z0; r.c0.c1 = z4; r.c0.c2 = z3;
-    r.c1.c0 = z2; r.c1.c1 = z1; r.c1.c2 = z5;
+    cpv(r.c0.c0, z0); cpv(r.c0.c1, z4); cpv(r.c0.c2, z3);
+    cpv(r.c1.c0, z2); cpv(r.c1.c1, z1); cpv(r.c1.c2, z5);
 }
 // conj(a^u), u = 4965661367192848881 (63 bits); value of src/fields/fq12.rs:121-124 + :249-266.
 // (The reference's multiply-by-one on the first set bit is skipped: same value.)
 BN_HD_NOINLINE void fq12_exp_by_neg_z(Fq12& r, const Fq12& a) {
     const uint64_t u = ((uint64_t)BN_U_HI << 32) | BN_U_LO;
-    Fq12 acc = a;  // bit 62
+    Fq12 acc;  // bit 62
+    cpv(acc, a);
     for (int i = 61; i >= 0; i--) {
         fq12_cyclotomic_sqr(acc, acc);
         if ((u >> i) & 1) fq12_mul(acc, acc, a);

@@ -52,9 +52,16 @@ class Prog:
         self.ntmp += 1
         return "t%d" % (self.ntmp - 1)
 
-    def emit(self, op, dst, *srcs):
-        self.ins.append((op, dst, srcs))
+    def emit(self, op, dst, *srcs, guard=None):
+        """guard: None or a predicate name like "%p0" / "!%p1" (instruction executes only if true)."""
+        self.ins.append((op, dst, srcs, guard))
         return dst
+
+    def label(self, name):
+        self.ins.append(("label", name, (), None))
+
+    def bra(self, name, guard=None):
+        self.ins.append(("bra", name, (), guard))
 
     # -- simulation -------------------------------------------------------------------------
     def run(self, env):
@@ -65,8 +72,26 @@ class Prog:
         def val(s):
             return s if isinstance(s, int) else env[s]
 
-        for op, dst, srcs in self.ins:
+        labels = {ins[1]: i for i, ins in enumerate(self.ins) if ins[0] == "label"}
+        pc = 0
+        while pc < len(self.ins):
+            op, dst, srcs, guard = self.ins[pc]
+            pc += 1
+            if op == "label":
+                continue
+            if guard is not None:
+                g = pred[guard.lstrip("!")]
+                if guard.startswith("!"):
+                    g = not g
+                if not g:
+                    continue
+            if op == "bra":
+                pc = labels[dst]
+                continue
             v = [val(s) for s in srcs if not (isinstance(s, str) and s.startswith("%p"))]
+            if op in ("setp.gt", "setp.eq", "setp.lt"):
+                pred[dst] = {"setp.gt": v[0] > v[1], "setp.eq": v[0] == v[1], "setp.lt": v[0] < v[1]}[op]
+                continue
             if op in ("mul.lo", "mul.hi"):
                 p = v[0] * v[1]
                 env[dst] = (p & M32) if op == "mul.lo" else (p >> 32)
@@ -120,7 +145,7 @@ class Prog:
         lines = []
         if self.ntmp:
             lines.append(".reg .u32 t<%d>;" % self.ntmp)
-        npred = len({d for op, d, _ in self.ins if op == "setp.ne"})
+        npred = len({d for op, d, _, _ in self.ins if op.startswith("setp")})
         if npred:
             lines.append(".reg .pred p<%d>;" % npred)
 
@@ -131,15 +156,22 @@ class Prog:
                 return s[1:]
             return opmap.get(s, s)
 
-        for op, dst, srcs in self.ins:
-            if op == "setp.ne":
-                lines.append("setp.ne.u32 %s, %s;" % (o(dst), ", ".join(o(s) for s in srcs)))
+        for op, dst, srcs, guard in self.ins:
+            g = ""
+            if guard is not None:
+                g = "@%s%s " % ("!" if guard.startswith("!") else "", guard.lstrip("!")[1:])
+            if op == "label":
+                lines.append("%s:" % dst)
+            elif op == "bra":
+                lines.append("%sbra %s;" % (g, dst))
+            elif op.startswith("setp"):
+                lines.append("%s%s.u32 %s, %s;" % (g, op, o(dst), ", ".join(o(s) for s in srcs)))
             elif op == "selp":
-                lines.append("selp.u32 %s, %s;" % (o(dst), ", ".join(o(s) for s in srcs)))
+                lines.append("%sselp.u32 %s, %s;" % (g, o(dst), ", ".join(o(s) for s in srcs)))
             elif op == "and":
-                lines.append("and.b32 %s, %s;" % (o(dst), ", ".join(o(s) for s in srcs)))
+                lines.append("%sand.b32 %s, %s;" % (g, o(dst), ", ".join(o(s) for s in srcs)))
             else:
-                lines.append("%s.u32 %s, %s;" % (op, o(dst), ", ".join(o(s) for s in srcs)))
+                lines.append("%s%s.u32 %s, %s;" % (g, op, o(dst), ", ".join(o(s) for s in srcs)))
         return lines
 
 
@@ -184,14 +216,19 @@ def chain(P, acc, pos, mults, fixed, carry_in, top_cannot_overflow=False):
 
 def cond_sub_q(P, r):
     """r (8 regs, value < 2q) -> r mod q, in place: t = r - q; keep t unless it borrowed."""
-    t = [P.tmp() for _ in range(8)]
+    # The top limb decides except when it equals q's top limb (probability 2^-32): only then is the full
+    # comparison run, behind a branch.  The subtraction itself is 8 predicated instructions, no selects.
+    P.emit("setp.gt", "%p0", r[7], QL[7])      # certainly >= q
+    P.emit("setp.eq", "%p1", r[7], QL[7])      # tie: compare the low 224 bits
+    P.bra("L_nt", guard="!%p1")
+    t = P.tmp()
+    for i in range(7):
+        P.emit(("sub.cc" if i == 0 else "subc.cc"), t, r[i], QL[i])
+    P.emit("subc", t, 0, 0)                    # 0xffffffff if low part < q's low part
+    P.emit("setp.eq", "%p0", t, 0)
+    P.label("L_nt")
     for i in range(8):
-        P.emit(("sub.cc" if i == 0 else "subc.cc"), t[i], r[i], QL[i])
-    m = P.tmp()
-    P.emit("subc", m, 0, 0)                    # 0xffffffff if r < q
-    P.emit("setp.ne", "%p0", m, 0)
-    for i in range(8):
-        P.emit("selp", r[i], r[i], t[i], "%p0")
+        P.emit(("sub.cc" if i == 0 else ("subc.cc" if i < 7 else "subc")), r[i], r[i], QL[i], guard="%p0")
 
 
 def gen_mul():
@@ -324,11 +361,9 @@ def gen_sub():
         P.emit("sub.cc" if i == 0 else "subc.cc", r[i], a[i], b[i])
     m = P.tmp()
     P.emit("subc", m, 0, 0)                    # all ones on borrow
-    qm = [P.tmp() for _ in range(8)]
-    for i in range(8):
-        P.emit("and", qm[i], m, QL[i])
+    P.emit("setp.ne", "%p0", m, 0)
     for i in range(8):                         # the final carry is the intended wrap of r - b + q past 2^256
-        P.emit("add.cc" if i == 0 else "addc.cc", r[i], r[i], qm[i])
+        P.emit("add.cc" if i == 0 else "addc.cc", r[i], r[i], QL[i], guard="%p0")
     return P
 
 
@@ -354,11 +389,9 @@ def gen_wide_sub():
         P.emit("sub.cc" if i == 0 else "subc.cc", a[i], a[i], b[i])
     m = P.tmp()
     P.emit("subc", m, 0, 0)
-    qm = [P.tmp() for _ in range(8)]
-    for i in range(8):
-        P.emit("and", qm[i], m, QL[i])
+    P.emit("setp.ne", "%p0", m, 0)
     for i in range(8):                         # final carry = intended wrap past 2^512
-        P.emit("add.cc" if i == 0 else "addc.cc", a[8 + i], a[8 + i], qm[i])
+        P.emit("add.cc" if i == 0 else "addc.cc", a[8 + i], a[8 + i], QL[i], guard="%p0")
     return P
 
 
@@ -389,6 +422,19 @@ def check():
             assert unl(pa.run(env), pa.outputs) == (a + b) % Q
             assert unl(ps.run(env), ps.outputs) == (a - b) % Q
             n += 1
+    # tie cases of the conditional subtraction: a + b has the same top limb as q
+    top = QL[7] << 224
+    for ssum in [Q - 2, Q - 1, Q, Q + 1, Q + 2, top, top + 1, Q + (1 << 100), Q - (1 << 100), top + (Q & ((1 << 224) - 1)) - 1,
+                 (top | ((1 << 224) - 1))] + [top + rng.randrange(1 << 224) for _ in range(200)]:
+        for _ in range(4):
+            lo = max(0, ssum - (Q - 1))
+            a = rng.randrange(lo, min(ssum, Q - 1) + 1)
+            b = ssum - a
+            assert 0 <= a < Q and 0 <= b < Q
+            env = {("a%d" % i): v for i, v in enumerate(limbs(a, 8))}
+            env.update({("b%d" % i): v for i, v in enumerate(limbs(b, 8))})
+            assert unl(pa.run(env), pa.outputs) == (a + b) % Q, ("add tie", hex(a), hex(b))
+            n += 1
     for _ in range(2000):
         t = rng.choice([rng.randrange(Q * R), Q * R - 1, 0, rng.randrange(Q) * rng.randrange(Q), (Q - 1) * (Q - 1),
                         rng.randrange(1 << 256), (rng.randrange(Q) << 256) | ((1 << 256) - 1)])
@@ -403,7 +449,7 @@ def check():
             assert unl(pwa.run(env), pwa.outputs) == t + u, "wide_add"
     print("simulated OK: %d mul/mulwide/add/sub pairs, 2000 redc/wide cases" % n)
     for p in (pm, pw, pr, pa, ps):
-        ops = [op.split(".")[0] for op, _, _ in p.ins]
+        ops = [op.split(".")[0] for op, _, _, _ in p.ins]
         print("  %-16s %3d PTX instrs (%d mad/mul)" % (p.name, len(p.ins), sum(o in ("mad", "madc", "mul") for o in ops)))
 
 
