@@ -4,6 +4,7 @@
 
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -31,6 +32,10 @@ struct bn254_ctx {
     int device;
     cudaStream_t stream;
     std::atomic<uint64_t> launches;
+    void* ws;          // grow-only device workspace (line-coefficient tables of the split Miller path)
+    size_t ws_bytes;
+    int split_miller;  // 1: three-kernel Miller path (default), 0: fused single kernel (BN254_FUSED_MILLER=1)
+    int split_fexp;    // 1: easy + hard final-exponentiation kernels (BN254_SPLIT_FEXP=1), 0: one kernel
 };
 struct bn254_g2precomp {
     int device;
@@ -97,6 +102,10 @@ int bn254_ctx_create(int device, bn254_ctx** out) {
     if (!c) return fail(BN254_ERR_NOMEM, "ctx alloc");
     c->device = device;
     c->launches = 0;
+    c->ws = nullptr;
+    c->ws_bytes = 0;
+    { const char* e = getenv("BN254_FUSED_MILLER"); c->split_miller = (e && e[0] == '1') ? 0 : 1; }
+    { const char* e = getenv("BN254_SPLIT_FEXP"); c->split_fexp = (e && e[0] == '1') ? 1 : 0; }
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { delete c; return fail(BN254_ERR_CUDA, "cudaStreamCreate", e); }
     // deep call chains (Fq12 -> Fq6 -> Fq2 noinline bodies) need more than the default stack
@@ -109,6 +118,7 @@ void bn254_ctx_destroy(bn254_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     cudaStreamDestroy(ctx->stream);
+    if (ctx->ws) cudaFree(ctx->ws);
     delete ctx;
 }
 int bn254_ctx_device(const bn254_ctx* ctx) { return ctx ? ctx->device : -1; }
@@ -120,6 +130,60 @@ int bn254_ctx_synchronize(bn254_ctx* ctx) {
 }
 uint64_t bn254_ctx_launch_count(const bn254_ctx* ctx) { return ctx ? ctx->launches.load() : 0; }
 
+}  // extern "C"
+// grow-only workspace: stream-ordered reuse is safe because every user enqueues on ctx->stream
+static int ctx_workspace(bn254_ctx* ctx, size_t bytes, void** out) {
+    if (bytes > ctx->ws_bytes) {
+        if (ctx->ws) { CU(cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->ws); ctx->ws = nullptr; ctx->ws_bytes = 0; }
+        cudaError_t e = cudaMalloc(&ctx->ws, bytes);
+        if (e != cudaSuccess) { ctx->ws = nullptr; return fail(BN254_ERR_NOMEM, "cudaMalloc workspace", e); }
+        ctx->ws_bytes = bytes;
+    }
+    *out = ctx->ws;
+    return 0;
+}
+// final exponentiation of n values (in place allowed): single kernel, or easy + hard kernels
+static int final_exp_dev(bn254_ctx* ctx, const Fq12* d_in, Fq12* d_out, uint8_t* d_some, uint8_t* d_is_one, size_t n) {
+    if (!ctx->split_fexp) {
+        LAUNCH(ctx, k_final_exp_many, n, d_in, d_out, d_some, d_is_one, n);
+        return 0;
+    }
+    // scratch: easy-part values + flags, placed after the Miller tables' use (stream-ordered, so reuse is safe)
+    void* ws = nullptr;
+    size_t vals = n * sizeof(Fq12);
+    TRY(ctx_workspace(ctx, vals + ((n + 15) & ~(size_t)15), &ws));
+    Fq12* t = (Fq12*)ws;
+    uint8_t* flags = (uint8_t*)ws + vals;
+    LAUNCH(ctx, k_final_exp_easy, n, d_in, t, flags, n);
+    LAUNCH(ctx, k_final_exp_hard, n, (const Fq12*)t, (const uint8_t*)flags, d_out, d_some, d_is_one, n);
+    return 0;
+}
+static const size_t MILLER_CHUNK = (size_t)1 << 17;   // pairings per table chunk (2.2 GB of line coefficients)
+// Miller values of n independent pairs (fused single kernel, or affine -> line table -> Miller from table)
+static int miller_many_dev(bn254_ctx* ctx, const G2* d_g2, const G1* d_g1, Fq12* d_f, uint8_t* d_ok, size_t n) {
+    if (!ctx->split_miller) {
+        LAUNCH(ctx, k_miller_many, n, d_g2, d_g1, d_f, d_ok, n);
+        return 0;
+    }
+    size_t chunk = n < MILLER_CHUNK ? n : MILLER_CHUNK;
+    size_t tab_bytes = (size_t)BN254_N_COEFFS * 12 * chunk * sizeof(uint4);
+    size_t qa_off = tab_bytes, pa_off = qa_off + chunk * sizeof(AffG2), ok_off = pa_off + chunk * sizeof(AffG1);
+    void* ws = nullptr;
+    TRY(ctx_workspace(ctx, ok_off + ((chunk + 15) & ~(size_t)15), &ws));
+    uint4* tab = (uint4*)ws;
+    AffG2* qa = (AffG2*)((char*)ws + qa_off);
+    AffG1* pa = (AffG1*)((char*)ws + pa_off);
+    uint8_t* ok = (uint8_t*)ws + ok_off;
+    for (size_t lo = 0; lo < n; lo += chunk) {
+        size_t m = n - lo < chunk ? n - lo : chunk;
+        LAUNCH(ctx, k_pairs_to_affine, m, d_g2 + lo, d_g1 + lo, qa, pa, ok, m);
+        LAUNCH(ctx, k_g2_lines_affine, m, (const AffG2*)qa, (const uint8_t*)ok, tab, m);
+        LAUNCH(ctx, k_miller_table_affine, m, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tab, d_f + lo, d_ok ? d_ok + lo : (uint8_t*)nullptr, m);
+    }
+    return 0;
+}
+extern "C" {
+
 // ---------------------------------------------------------------------------------------------
 // pairing
 // ---------------------------------------------------------------------------------------------
@@ -128,8 +192,8 @@ int bn254_pairing_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_g2, v
     if (n == 0) return 0;
     if (!d_g1 || !d_g2 || !d_gt_out) return fail(BN254_ERR_ARG, "null pointer");
     // Miller values are written to the output buffer and exponentiated in place
-    LAUNCH(ctx, k_miller_many, n, (const G2*)d_g2, (const G1*)d_g1, (Fq12*)d_gt_out, (uint8_t*)nullptr, n);
-    LAUNCH(ctx, k_final_exp_many, n, (const Fq12*)d_gt_out, (Fq12*)d_gt_out, (uint8_t*)nullptr, (uint8_t*)nullptr, n);
+    TRY(miller_many_dev(ctx, (const G2*)d_g2, (const G1*)d_g1, (Fq12*)d_gt_out, (uint8_t*)nullptr, n));
+    TRY(final_exp_dev(ctx, (const Fq12*)d_gt_out, (Fq12*)d_gt_out, (uint8_t*)nullptr, (uint8_t*)nullptr, n));
     return 0;
 }
 int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_out, size_t n) {
@@ -150,7 +214,7 @@ int bn254_miller_loop_many_dev(bn254_ctx* ctx, const void* d_g2, const void* d_g
     TRY(use(ctx));
     if (n == 0) return 0;
     if (!d_g1 || !d_g2 || !d_gt_out) return fail(BN254_ERR_ARG, "null pointer");
-    LAUNCH(ctx, k_miller_many, n, (const G2*)d_g2, (const G1*)d_g1, (Fq12*)d_gt_out, d_ok, n);
+    TRY(miller_many_dev(ctx, (const G2*)d_g2, (const G1*)d_g1, (Fq12*)d_gt_out, d_ok, n));
     return 0;
 }
 int bn254_miller_loop_many(bn254_ctx* ctx, const void* g2, const void* g1, void* gt_out, uint8_t* ok, size_t n) {
@@ -217,7 +281,7 @@ int bn254_pairing_product_many_dev(bn254_ctx* ctx, const void* d_g1, const void*
     Fq12* d_f = (Fq12*)d_gt_out;
     if (!d_f) { TRY(f.alloc(n_checks * sizeof(Fq12))); d_f = f.as<Fq12>(); }
     TRY(miller_products_dev(ctx, (const G1*)d_g1, (const G2*)d_g2, pairs_per_check, nullptr, nullptr, n_checks, d_f));
-    LAUNCH(ctx, k_final_exp_many, n_checks, (const Fq12*)d_f, d_gt_out ? d_f : (Fq12*)nullptr, (uint8_t*)nullptr, d_is_one, n_checks);
+    TRY(final_exp_dev(ctx, (const Fq12*)d_f, d_gt_out ? d_f : (Fq12*)nullptr, (uint8_t*)nullptr, d_is_one, n_checks));
     if (!d_gt_out) CU(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
@@ -276,7 +340,7 @@ int bn254_final_exp_many_dev(bn254_ctx* ctx, const void* d_in, void* d_out, uint
     TRY(use(ctx));
     if (n == 0) return 0;
     if (!d_in || !d_out) return fail(BN254_ERR_ARG, "null pointer");
-    LAUNCH(ctx, k_final_exp_many, n, (const Fq12*)d_in, (Fq12*)d_out, d_some, (uint8_t*)nullptr, n);
+    TRY(final_exp_dev(ctx, (const Fq12*)d_in, (Fq12*)d_out, d_some, (uint8_t*)nullptr, n));
     return 0;
 }
 int bn254_final_exp_many(bn254_ctx* ctx, const void* gt_in, void* gt_out, uint8_t* some, size_t n) {
@@ -465,7 +529,7 @@ int bn254_pairing_product_precomp_many_dev(bn254_ctx* ctx, const bn254_g2precomp
     Fq12* d_f = (Fq12*)d_gt_out;
     if (!d_f) { TRY(f.alloc(n_checks * sizeof(Fq12))); d_f = f.as<Fq12>(); }
     TRY(miller_products_dev(ctx, (const G1*)d_g1v, (const G2*)d_g2v, v, (const G1*)d_g1s, pc, n_checks, d_f));
-    LAUNCH(ctx, k_final_exp_many, n_checks, (const Fq12*)d_f, d_gt_out ? d_f : (Fq12*)nullptr, (uint8_t*)nullptr, d_is_one, n_checks);
+    TRY(final_exp_dev(ctx, (const Fq12*)d_f, d_gt_out ? d_f : (Fq12*)nullptr, (uint8_t*)nullptr, d_is_one, n_checks));
     if (!d_gt_out) CU(cudaStreamSynchronize(ctx->stream));
     return 0;
 }

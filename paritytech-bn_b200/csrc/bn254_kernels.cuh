@@ -79,6 +79,31 @@ BN_KERNEL k_final_exp_many(const Fq12* __restrict__ in, Fq12* __restrict__ out, 
     }
 }
 
+// final exponentiation as two kernels: the easy part carries the inversion / Frobenius code (cold), the hard
+// part is the x^u loops; keeping the cold code out of the hard-part kernel keeps its hot SASS contiguous.
+BN_KERNEL k_final_exp_easy(const Fq12* __restrict__ in, Fq12* __restrict__ out, uint8_t* __restrict__ some, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Fq12 f = in[i], r;
+    bool s = fq12_final_exp_first_chunk(r, f);
+    out[i] = r;
+    some[i] = s ? 1 : 0;
+}
+BN_KERNEL k_final_exp_hard(const Fq12* __restrict__ in, const uint8_t* __restrict__ some_in, Fq12* __restrict__ out,
+                           uint8_t* __restrict__ some, uint8_t* __restrict__ is_one, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    bool s = some_in[i] != 0;
+    Fq12 f = in[i], r;
+    if (s) fq12_final_exp_last_chunk(r, f); else r = fq12_zero();
+    if (out) out[i] = r;
+    if (some) some[i] = s ? 1 : 0;
+    if (is_one) {
+        Fq12 one = fq12_one();
+        is_one[i] = fq12_eq(r, one) ? 1 : 0;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // product checks: one thread per check, shared squaring chain (groups::miller_loop_batch,
 // src/groups/mod.rs:609-640), line coefficients of the variable G2 points produced on the fly,
@@ -151,6 +176,24 @@ BN_KERNEL k_miller_product(const G1* __restrict__ g1v, const G2* __restrict__ g2
     f_out[i] = f;
 }
 
+// ---------------------------------------------------------------------------------------------
+// split Miller path (three kernels, each with < 32 KB of hot SASS so the loop bodies stay resident in
+// the SM's 32 KB L1.5 instruction cache): (1) joint affine conversion, (2) line coefficients of Q_i
+// into the word-major table (coalesced 16-byte stores), (3) f_i from table i and P_i.
+// The table makes one trip through HBM: 16,704 B written + read per pairing (~2.2 GB per 2^16 batch).
+// ---------------------------------------------------------------------------------------------
+BN_KERNEL k_pairs_to_affine(const G2* __restrict__ q, const G1* __restrict__ p, AffG2* __restrict__ qa_out,
+                            AffG1* __restrict__ pa_out, uint8_t* __restrict__ ok, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    G1 pp = p[i];
+    G2 qq = q[i];
+    AffG1 pa;
+    AffG2 qa;
+    bool good = pair_to_affine(pa, qa, pp, qq);
+    if (good) { qa_out[i] = qa; pa_out[i] = pa; }
+    ok[i] = good ? 1 : 0;
+}
 // pair i against table i (materialised-G2Precomp streaming variant: coalesced table reads)
 BN_KERNEL k_miller_precomp_each(const G1* __restrict__ g1, const uint4* __restrict__ tab, size_t n_tables,
                                 Fq12* __restrict__ f_out, uint8_t* __restrict__ ok, size_t n) {
@@ -198,6 +241,36 @@ BN_KERNEL k_g2_precompute(const G2* __restrict__ q, uint4* __restrict__ tab, Aff
     TableSink s;
     s.tab = tab; s.n_tables = n; s.j = i; s.idx = 0;
     g2_walk_lines(qa, s);
+}
+
+BN_KERNEL k_g2_lines_affine(const AffG2* __restrict__ qa, const uint8_t* __restrict__ ok, uint4* __restrict__ tab, size_t n) {
+    size_t i = gtid();
+    if (i >= n || !ok[i]) return;
+    AffG2 q = qa[i];
+    TableSink s;
+    s.tab = tab; s.n_tables = n; s.j = i; s.idx = 0;
+    g2_walk_lines(q, s);
+}
+BN_KERNEL k_miller_table_affine(const AffG1* __restrict__ pa_in, const uint8_t* __restrict__ ok_in, const uint4* __restrict__ tab,
+                                Fq12* __restrict__ f_out, uint8_t* __restrict__ ok_out, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Fq12 f = fq12_one();
+    bool good = ok_in[i] != 0;
+    if (good) {
+        AffG1 pa = pa_in[i];
+        EllCoeffs c;
+        int idx = 0;
+        for (int k = 0; k < 64; k++) {
+            if (k) fq12_sqr(f, f);
+            load_coeff(c, tab, n, i, idx++); line_mul(f, c, pa);
+            if (naf_digit(k)) { load_coeff(c, tab, n, i, idx++); line_mul(f, c, pa); }
+        }
+        load_coeff(c, tab, n, i, idx++); line_mul(f, c, pa);
+        load_coeff(c, tab, n, i, idx++); line_mul(f, c, pa);
+    }
+    f_out[i] = f;
+    if (ok_out) ok_out[i] = good ? 1 : 0;
 }
 
 // out[g] = prod_{j < group} in[g*group + j]
