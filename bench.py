@@ -35,6 +35,18 @@ FQMUL_MILLER = 2916 + 6045                # lean Fq-mul: precompute + Miller loo
 FQMUL_FINALEXP = 228 + 8541               # easy + hard part
 FQMUL_PAIRING = FQMUL_MILLER + FQMUL_FINALEXP   # 17,730
 G1, G2, GT = 96, 192, 384
+# dram__bytes_read.sum + dram__bytes_write.sum per pairing (per launch / 2^16) from profiles/r01_ncu_full_pairing_v3.md
+NCU_DRAM_BYTES_PER_PAIRING = {}
+try:
+    with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as _f:
+        NCU_DRAM_BYTES_PER_PAIRING = json.load(_f)
+except Exception:
+    pass
+try:
+    with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as _f:
+        HBM_PEAK_GBS = json.load(_f).get("hbm_gbs")
+except Exception:
+    HBM_PEAK_GBS = 6538.6   # fallback: the figure the driver measured on this pool (B200_PROFILING.md)
 
 
 def parse():
@@ -44,7 +56,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch-log2", type=int, default=16, help="pairings per GPU per step = 2^k")
-    ap.add_argument("--variant", default=None, help="library variant suffix ('' or '_r255')")
+    ap.add_argument("--variant", default=None, help="library variant suffix (ad hoc A/B builds)")
     ap.add_argument("--cpu-sample", type=int, default=4096, help="pairings in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--extra", action="store_true", help="also time Groth16 checks and scalar muls (extra keys)")
@@ -212,23 +224,21 @@ def main():
     total_ms = sum(a.elapsed_time(b) for a, b in ev)
     clocks = sampler.stop() if rank == 0 else None
 
-    # ---- per-kernel split for the roofline (same inputs, separate launches) -----------------------------------
-    def timed(fn, reps=3):
-        best = None
-        for _ in range(reps):
-            l2_flush()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record(stream); fn(); b.record(stream)
-            torch.cuda.synchronize()
-            t = a.elapsed_time(b)
-            best = t if best is None else min(best, t)
-        return best
-    lib = eng.lib
+    # ---- per-kernel split for the roofline: the profiling twin of the same entry point (identical launches,
+    # each kernel bracketed by CUDA events on the library's stream) ------------------------------------------------
     import ctypes
-    t_miller = timed(lambda: eng._check(lib.bn254_miller_loop_many_dev(eng.ctx, ctypes.c_void_p(d_g2.data_ptr()), ctypes.c_void_p(d_g1.data_ptr()),
-                                                                      ctypes.c_void_p(d_ml.data_ptr()), None, ctypes.c_size_t(n))))
-    t_fexp = timed(lambda: eng._check(lib.bn254_final_exp_many_dev(eng.ctx, ctypes.c_void_p(d_ml.data_ptr()), ctypes.c_void_p(d_out.data_ptr()),
-                                                                  None, ctypes.c_size_t(n))))
+    lib = eng.lib
+    best = None
+    for _ in range(3):
+        l2_flush()
+        ms4 = (ctypes.c_float * 4)()
+        eng._check(lib.bn254_pairing_many_dev_timed(eng.ctx, ctypes.c_void_p(d_g1.data_ptr()), ctypes.c_void_p(d_g2.data_ptr()),
+                                                    ctypes.c_void_p(d_out.data_ptr()), ctypes.c_size_t(n), ms4))
+        cur = [float(x) for x in ms4]
+        if best is None or sum(cur) < sum(best):
+            best = cur
+    t_aff, t_lines, t_mtab, t_fexp = best
+    t_miller = t_aff + t_lines + t_mtab
 
     # ---- e2e: public host-buffer API, pinned host memory, H2D + D2H inside the timed region ----------------------
     h_g1 = torch.empty(n * G1, dtype=torch.uint8, pin_memory=True); h_g1.copy_(d_g1)
@@ -252,10 +262,11 @@ def main():
         micro[nm] = ops / (ms * 1e-3)
 
     # ---- aggregate over ranks ---------------------------------------------------------------------------------------
-    t = torch.tensor([total_ms, e2e_s, t_miller, t_fexp], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, e2e_s, t_aff, t_lines, t_mtab, t_fexp], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_s, t_miller, t_fexp = [float(x) for x in t.tolist()]
+    total_ms, e2e_s, t_aff, t_lines, t_mtab, t_fexp = [float(x) for x in t.tolist()]
+    t_miller = t_aff + t_lines + t_mtab
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -266,8 +277,14 @@ def main():
     # IMAD-equivalent peak: a wide multiply counts 2; use the better of the two measured forms
     peak_measured = max(micro["imad"], 2.0 * micro["imad_wide"])
     sm_mhz = (clocks or {}).get("sm_mhz") or 0.0
-    dom_name, dom_ms, dom_fq = ("k_final_exp_many", t_fexp, FQMUL_FINALEXP) if t_fexp >= t_miller else ("k_miller_many", t_miller, FQMUL_MILLER)
+    # dominant kernel = the longest launch of the step; its algorithmic work in lean Fq multiplications
+    cands = [("k_final_exp_many", t_fexp, FQMUL_FINALEXP), ("k_miller_table_affine", t_mtab, 6045), ("k_g2_lines_affine", t_lines, 2916)]
+    if t_lines == 0.0:
+        cands = [("k_final_exp_many", t_fexp, FQMUL_FINALEXP), ("k_miller_many", t_mtab, FQMUL_MILLER)]
+    dom_name, dom_ms, dom_fq = max(cands, key=lambda c: c[1])
     achieved = dom_fq * FQMUL_IMAD_EQ * n / (dom_ms * 1e-3)
+    table_bytes = 87 * 192 * n
+    traffic = NCU_DRAM_BYTES_PER_PAIRING.get(dom_name)
     out = {
         "metric": "BN254 pairings/sec", "value": value, "unit": "pairings/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -280,12 +297,20 @@ def main():
                 "api": "Engine.pairing -> bn254_pairing_many (pinned host buffers)"},
         "gpu_launches": int(launches),
         "roofline": {"bound": "imad", "kernel": dom_name, "achieved": achieved / 1e12, "peak": peak_measured / 1e12, "unit": "TIMAD-eq/s",
-                     "frac": achieved / peak_measured, "traffic": None,
-                     "peak_source": "measured in this run (register-only mad.lo / mad.wide chains); MEASURED_PEAKS.json has no integer peak",
+                     "frac": achieved / peak_measured,
+                     "traffic": traffic * n if traffic else None,
+                     "traffic_note": "dram read+write bytes per launch of that kernel from the committed ncu --set full capture (profiles/), scaled to this batch; "
+                                     "algorithmic bytes per launch = %d (Gt in + Gt out)" % (2 * GT * n),
+                     "peak_source": "measured in this run (register-only mad.lo chains, 64 IMAD/clk/SM); an IMAD.WIDE counts 2 IMAD-eq (measured 4.1 clk/warp-inst "
+                                    "vs 2.0 for IMAD, profiles/r01_pipe_microbench2.txt); MEASURED_PEAKS.json has no integer peak",
                      "peak_theoretical": sms * 64 * sm_mhz * 1e6 / 1e12 if sm_mhz else None,
                      "algorithmic_imad_eq_per_pairing": FQMUL_PAIRING * FQMUL_IMAD_EQ,
                      "whole_step_frac": FQMUL_PAIRING * FQMUL_IMAD_EQ * n * world * args.steps / (total_ms * 1e-3) / (peak_measured * world),
-                     "kernels_ms": {"k_miller_many": t_miller, "k_final_exp_many": t_fexp},
+                     "kernels_ms": {"k_pairs_to_affine": t_aff, "k_g2_lines_affine": t_lines, "k_miller_table_affine": t_mtab, "k_final_exp_many": t_fexp,
+                                    "k_miller_many": t_miller},
+                     "g2precomp_stream_hbm_gbs": {"write_k_g2_lines_affine": table_bytes / (t_lines * 1e-3) / 1e9 if t_lines else None,
+                                                  "read_k_miller_table_affine": table_bytes / (t_mtab * 1e-3) / 1e9 if t_mtab else None,
+                                                  "bytes": table_bytes, "hbm_peak_gbs": HBM_PEAK_GBS},
                      "microbench_ops_per_s": micro},
     }
     if not args.no_cpu_baseline:

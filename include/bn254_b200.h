@@ -69,6 +69,11 @@ const char* bn254_build_info(void);
 int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_out, size_t n);
 int bn254_pairing_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_g2, void* d_gt_out, size_t n);
 
+/* Profiling twin of bn254_pairing_many_dev: identical launches, each kernel bracketed by CUDA events on the
+ * context's stream.  ms[4] = {affine conversion, G2 line table, Miller loop from table, final exponentiation}
+ * in milliseconds (fused-Miller build: ms[0] = ms[1] = 0, ms[2] = the fused kernel).  Synchronises. */
+int bn254_pairing_many_dev_timed(bn254_ctx* ctx, const void* d_g1, const void* d_g2, void* d_gt_out, size_t n, float* ms);
+
 /* ---- pairing_batch: src/lib.rs:615-623 `pairing_batch(&[(G1, G2)]) -> Gt` ---------------------- */
 /* n_checks independent products of pairs_per_check pairs each (pair j of check i at index
  * i*pairs_per_check + j), ONE final exponentiation per check.  Pairs with a point at infinity are
@@ -88,6 +93,11 @@ int bn254_miller_loop_batch(bn254_ctx* ctx, const void* g2, const void* g1, size
 int bn254_miller_loop_many(bn254_ctx* ctx, const void* g2, const void* g1, void* gt_out, uint8_t* ok, size_t n);
 int bn254_miller_loop_many_dev(bn254_ctx* ctx, const void* d_g2, const void* d_g1, void* d_gt_out, uint8_t* d_ok,
                                size_t n);
+
+/* Un-exponentiated product of the Miller values of n pairs with pairing_batch's skip semantics (a pair with a
+ * point at infinity contributes one; n = 0 yields one).  This is the per-GPU partial of a product sharded over
+ * several processes / devices: partials multiply exactly (src/groups/mod.rs:609-640). */
+int bn254_miller_product(bn254_ctx* ctx, const void* g1, const void* g2, size_t n, void* gt_out);
 
 /* ---- Gt: src/lib.rs:584-609 -------------------------------------------------------------------- */
 /* Gt::final_exponentiation -> Option<Gt>: some[i] = 0 (and gt_out = 0) iff the input is zero */

@@ -215,6 +215,17 @@ def miller_loop_many(q, p, threads=0):
     return out, ok
 
 
+def miller_loop_batch_skip(q, p):
+    """Un-exponentiated Miller product with pairing_batch's skip semantics (pairs with a point at infinity
+    contribute one; empty -> one): product of the single Miller values, src/groups/mod.rs:609-640."""
+    vals, _ok = miller_loop_many(q, p)
+    acc = np.frombuffer(((1 << 256) % 0x30644e72e131a029b85045b68181585d97816a916871ca8d3c208c16d87cfd47).to_bytes(32, "little") + bytes(352),
+                        dtype=np.uint8).copy()
+    for i in range(vals.size // FQ12):
+        acc = fq12_mul(acc, vals[i * FQ12:(i + 1) * FQ12])
+    return acc
+
+
 def constants():
     """Raw dump of the derived constants (order: see orc_constants in bn254_oracle.c)."""
     buf = np.zeros(4096, dtype=np.uint8)

@@ -175,6 +175,21 @@ class Engine:
         self._check(self.lib.bn254_miller_loop_batch(self.ctx, _p(g2), _p(g1), ctypes.c_size_t(n), _p(out)))
         return out
 
+    def miller_product(self, g1, g2):
+        """Un-exponentiated product of the Miller values of all pairs, pairing_batch skip semantics
+        (the per-GPU partial of a sharded product)."""
+        g1, n = _arr(g1, G1_BYTES)
+        g2, n2 = _arr(g2, G2_BYTES)
+        assert n == n2
+        out = np.empty(GT_BYTES, dtype=np.uint8)
+        self._check(self.lib.bn254_miller_product(self.ctx, _p(g1) if n else None, _p(g2) if n else None, ctypes.c_size_t(n), _p(out)))
+        return out
+
+    def gt_one(self):
+        """Gt::one() (src/lib.rs:588) = the empty product."""
+        e = np.empty(0, dtype=np.uint8)
+        return self.miller_product(e, e)
+
     def miller_loop_many(self, g2, g1):
         g2, n = _arr(g2, G2_BYTES)
         g1, n1 = _arr(g1, G1_BYTES)

@@ -32,6 +32,8 @@ struct bn254_ctx {
     int device;
     cudaStream_t stream;
     std::atomic<uint64_t> launches;
+    void* io;          // grow-only device arena for the host-pointer entry points (no cudaMalloc per call)
+    size_t io_bytes;
     void* ws;          // grow-only device workspace (line-coefficient tables of the split Miller path)
     size_t ws_bytes;
     int split_miller;  // 1: three-kernel Miller path (default), 0: fused single kernel (BN254_FUSED_MILLER=1)
@@ -104,6 +106,8 @@ int bn254_ctx_create(int device, bn254_ctx** out) {
     c->launches = 0;
     c->ws = nullptr;
     c->ws_bytes = 0;
+    c->io = nullptr;
+    c->io_bytes = 0;
     { const char* e = getenv("BN254_FUSED_MILLER"); c->split_miller = (e && e[0] == '1') ? 0 : 1; }
     { const char* e = getenv("BN254_SPLIT_FEXP"); c->split_fexp = (e && e[0] == '1') ? 1 : 0; }
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
@@ -119,6 +123,7 @@ void bn254_ctx_destroy(bn254_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     cudaStreamDestroy(ctx->stream);
     if (ctx->ws) cudaFree(ctx->ws);
+    if (ctx->io) cudaFree(ctx->io);
     delete ctx;
 }
 int bn254_ctx_device(const bn254_ctx* ctx) { return ctx ? ctx->device : -1; }
@@ -156,6 +161,20 @@ static int final_exp_dev(bn254_ctx* ctx, const Fq12* d_in, Fq12* d_out, uint8_t*
     uint8_t* flags = (uint8_t*)ws + vals;
     LAUNCH(ctx, k_final_exp_easy, n, d_in, t, flags, n);
     LAUNCH(ctx, k_final_exp_hard, n, (const Fq12*)t, (const uint8_t*)flags, d_out, d_some, d_is_one, n);
+    return 0;
+}
+// I/O arena of the synchronous host-pointer entry points: carve `count` 256-byte-aligned regions
+static int ctx_io(bn254_ctx* ctx, const size_t* sizes, int count, void** out) {
+    size_t total = 0;
+    for (int i = 0; i < count; i++) total += (sizes[i] + 255) & ~(size_t)255;
+    if (total > ctx->io_bytes) {
+        if (ctx->io) { CU(cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->io); ctx->io = nullptr; ctx->io_bytes = 0; }
+        cudaError_t e = cudaMalloc(&ctx->io, total);
+        if (e != cudaSuccess) { ctx->io = nullptr; return fail(BN254_ERR_NOMEM, "cudaMalloc I/O arena", e); }
+        ctx->io_bytes = total;
+    }
+    char* p = (char*)ctx->io;
+    for (int i = 0; i < count; i++) { out[i] = p; p += (sizes[i] + 255) & ~(size_t)255; }
     return 0;
 }
 static const size_t MILLER_CHUNK = (size_t)1 << 17;   // pairings per table chunk (2.2 GB of line coefficients)
@@ -196,16 +215,69 @@ int bn254_pairing_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_g2, v
     TRY(final_exp_dev(ctx, (const Fq12*)d_gt_out, (Fq12*)d_gt_out, (uint8_t*)nullptr, (uint8_t*)nullptr, n));
     return 0;
 }
+int bn254_pairing_many_dev_timed(bn254_ctx* ctx, const void* d_g1, const void* d_g2, void* d_gt_out, size_t n, float* ms) {
+    TRY(use(ctx));
+    if (!ms) return fail(BN254_ERR_ARG, "null pointer");
+    ms[0] = ms[1] = ms[2] = ms[3] = 0.f;
+    if (n == 0) return 0;
+    if (!d_g1 || !d_g2 || !d_gt_out) return fail(BN254_ERR_ARG, "null pointer");
+    cudaEvent_t ev[5];
+    for (int i = 0; i < 5; i++) CU(cudaEventCreate(&ev[i]));
+    const G1* g1 = (const G1*)d_g1;
+    const G2* g2 = (const G2*)d_g2;
+    Fq12* f = (Fq12*)d_gt_out;
+    auto body = [&]() -> int {
+        if (!ctx->split_miller) {
+            CU(cudaEventRecord(ev[0], ctx->stream));
+            LAUNCH(ctx, k_miller_many, n, g2, g1, f, (uint8_t*)nullptr, n);
+            CU(cudaEventRecord(ev[1], ctx->stream));
+            CU(cudaEventSynchronize(ev[1]));
+            float t; CU(cudaEventElapsedTime(&t, ev[0], ev[1])); ms[2] = t;
+        } else {
+            size_t chunk = n < MILLER_CHUNK ? n : MILLER_CHUNK;
+            size_t tab_bytes = (size_t)BN254_N_COEFFS * 12 * chunk * sizeof(uint4);
+            size_t qa_off = tab_bytes, pa_off = qa_off + chunk * sizeof(AffG2), ok_off = pa_off + chunk * sizeof(AffG1);
+            void* ws = nullptr;
+            TRY(ctx_workspace(ctx, ok_off + ((chunk + 15) & ~(size_t)15), &ws));
+            uint4* tab = (uint4*)ws;
+            AffG2* qa = (AffG2*)((char*)ws + qa_off);
+            AffG1* pa = (AffG1*)((char*)ws + pa_off);
+            uint8_t* ok = (uint8_t*)ws + ok_off;
+            for (size_t lo = 0; lo < n; lo += chunk) {
+                size_t m = n - lo < chunk ? n - lo : chunk;
+                CU(cudaEventRecord(ev[0], ctx->stream));
+                LAUNCH(ctx, k_pairs_to_affine, m, g2 + lo, g1 + lo, qa, pa, ok, m);
+                CU(cudaEventRecord(ev[1], ctx->stream));
+                LAUNCH(ctx, k_g2_lines_affine, m, (const AffG2*)qa, (const uint8_t*)ok, tab, m);
+                CU(cudaEventRecord(ev[2], ctx->stream));
+                LAUNCH(ctx, k_miller_table_affine, m, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tab, f + lo, (uint8_t*)nullptr, m);
+                CU(cudaEventRecord(ev[3], ctx->stream));
+                CU(cudaEventSynchronize(ev[3]));
+                for (int i = 0; i < 3; i++) { float t; CU(cudaEventElapsedTime(&t, ev[i], ev[i + 1])); ms[i] += t; }
+            }
+        }
+        CU(cudaEventRecord(ev[3], ctx->stream));
+        TRY(final_exp_dev(ctx, (const Fq12*)f, f, (uint8_t*)nullptr, (uint8_t*)nullptr, n));
+        CU(cudaEventRecord(ev[4], ctx->stream));
+        CU(cudaEventSynchronize(ev[4]));
+        float t; CU(cudaEventElapsedTime(&t, ev[3], ev[4])); ms[3] = t;
+        return 0;
+    };
+    int rc = body();
+    for (int i = 0; i < 5; i++) cudaEventDestroy(ev[i]);
+    return rc;
+}
 int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_out, size_t n) {
     TRY(use(ctx));
     if (n == 0) return 0;
     if (!g1 || !g2 || !gt_out) return fail(BN254_ERR_ARG, "null pointer");
-    DevBuf a, b, o;
-    TRY(a.alloc(n * sizeof(G1))); TRY(b.alloc(n * sizeof(G2))); TRY(o.alloc(n * sizeof(Fq12)));
-    TRY(h2d(ctx, a.p, g1, n * sizeof(G1)));
-    TRY(h2d(ctx, b.p, g2, n * sizeof(G2)));
-    TRY(bn254_pairing_many_dev(ctx, a.p, b.p, o.p, n));
-    TRY(d2h(ctx, gt_out, o.p, n * sizeof(Fq12)));
+    size_t sz[3] = {n * sizeof(G1), n * sizeof(G2), n * sizeof(Fq12)};
+    void* d[3];
+    TRY(ctx_io(ctx, sz, 3, d));
+    TRY(h2d(ctx, d[0], g1, sz[0]));
+    TRY(h2d(ctx, d[1], g2, sz[1]));
+    TRY(bn254_pairing_many_dev(ctx, d[0], d[1], d[2], n));
+    TRY(d2h(ctx, gt_out, d[2], sz[2]));
     CU(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
@@ -291,13 +363,14 @@ int bn254_pairing_product_many(bn254_ctx* ctx, const void* g1, const void* g2, s
     if (n_checks == 0) return 0;
     size_t n = pairs_per_check * n_checks;
     if (n && (!g1 || !g2)) return fail(BN254_ERR_ARG, "null pointer");
-    DevBuf a, b, o, k;
-    TRY(a.alloc(n * sizeof(G1))); TRY(b.alloc(n * sizeof(G2))); TRY(o.alloc(n_checks * sizeof(Fq12))); TRY(k.alloc(n_checks));
-    TRY(h2d(ctx, a.p, g1, n * sizeof(G1)));
-    TRY(h2d(ctx, b.p, g2, n * sizeof(G2)));
-    TRY(bn254_pairing_product_many_dev(ctx, a.p, b.p, pairs_per_check, n_checks, o.p, k.as<uint8_t>()));
-    if (gt_out) TRY(d2h(ctx, gt_out, o.p, n_checks * sizeof(Fq12)));
-    if (is_one) TRY(d2h(ctx, is_one, k.p, n_checks));
+    size_t sz[4] = {n * sizeof(G1), n * sizeof(G2), n_checks * sizeof(Fq12), n_checks};
+    void* d[4];
+    TRY(ctx_io(ctx, sz, 4, d));
+    TRY(h2d(ctx, d[0], g1, sz[0]));
+    TRY(h2d(ctx, d[1], g2, sz[1]));
+    TRY(bn254_pairing_product_many_dev(ctx, d[0], d[1], pairs_per_check, n_checks, d[2], (uint8_t*)d[3]));
+    if (gt_out) TRY(d2h(ctx, gt_out, d[2], sz[2]));
+    if (is_one) TRY(d2h(ctx, is_one, d[3], n_checks));
     CU(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
@@ -328,6 +401,29 @@ int bn254_miller_loop_batch(bn254_ctx* ctx, const void* g2, const void* g1, size
         if (!ok[i]) return BN254_ERR_TO_AFFINE;   // Err(CurveError::ToAffineConversion), src/lib.rs:629-630
     Fq12* res = nullptr;
     TRY(tree_product(ctx, f.as<Fq12>(), s.as<Fq12>(), n, &res));
+    TRY(d2h(ctx, gt_out, res, sizeof(Fq12)));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int bn254_miller_product(bn254_ctx* ctx, const void* g1, const void* g2, size_t n, void* gt_out) {
+    TRY(use(ctx));
+    if (!gt_out) return fail(BN254_ERR_ARG, "null pointer");
+    if (n && (!g1 || !g2)) return fail(BN254_ERR_ARG, "null pointer");
+    size_t cnt = n ? n : 1;
+    size_t sz[4] = {cnt * sizeof(G1), cnt * sizeof(G2), cnt * sizeof(Fq12), ((cnt + 1) / 2) * sizeof(Fq12)};
+    void* d[4];
+    TRY(ctx_io(ctx, sz, 4, d));
+    Fq12* res = (Fq12*)d[2];
+    if (n == 0) {
+        LAUNCH(ctx, (k_miller_product<1, 4>), 1, (const G1*)nullptr, (const G2*)nullptr, 0, (const G1*)nullptr,
+               (const uint4*)nullptr, 0, res, (size_t)1);
+    } else {
+        TRY(h2d(ctx, d[0], g1, sz[0]));
+        TRY(h2d(ctx, d[1], g2, sz[1]));
+        TRY(miller_many_dev(ctx, (const G2*)d[1], (const G1*)d[0], (Fq12*)d[2], (uint8_t*)nullptr, n));
+        TRY(tree_product(ctx, (Fq12*)d[2], (Fq12*)d[3], n, &res));
+    }
     TRY(d2h(ctx, gt_out, res, sizeof(Fq12)));
     CU(cudaStreamSynchronize(ctx->stream));
     return 0;

@@ -269,3 +269,82 @@ def test_sharded_product(eng):
     assert not is_one and out.tobytes() == c.pairing_batch(g1, g2).tobytes()
     for e in engines[1:]:
         e.close()
+
+
+def test_conditional_subtraction_tie_cases(eng):
+    """The predicated conditional subtraction decides on the top limb and takes a rare exact path when it ties
+    with q's top limb: sums / differences / products landing in [q_top << 224, (q_top + 1) << 224)."""
+    rng = np.random.default_rng(77)
+    top = (o.Q >> 224) << 224
+    sums = [o.Q - 2, o.Q - 1, o.Q, o.Q + 1, o.Q + 2, top, top + 1, (top | ((1 << 224) - 1))]
+    sums += [top + int(rng.integers(0, 2**62)) * (1 << 160) + int(rng.integers(0, 2**62)) for _ in range(504)]
+    aa, bb = [], []
+    for s in sums:
+        lo = max(0, s - (o.Q - 1))
+        a = lo + (int(rng.integers(0, 2**62)) * (1 << 190)) % (min(s, o.Q - 1) - lo + 1)
+        aa.append(a); bb.append(s - a)
+    a = np.frombuffer(b"".join(v.to_bytes(32, "little") for v in aa), dtype=np.uint8).copy()   # raw Montgomery images
+    b = np.frombuffer(b"".join(v.to_bytes(32, "little") for v in bb), dtype=np.uint8).copy()
+    assert eng.field_op("fq_add", a, b).tobytes() == c.fq_add(a, b).tobytes()
+    assert eng.field_op("fq_sub", a, b).tobytes() == c.fq_sub(a, b).tobytes()
+    assert eng.field_op("fq_sub", b, a).tobytes() == c.fq_sub(b, a).tobytes()
+    assert eng.field_op("fq_mul", a, b).tobytes() == c.fq_mul(a, b).tobytes()
+
+
+def test_fused_and_split_miller_paths_agree(eng):
+    """Both Miller implementations (single fused kernel; affine -> line table -> Miller-from-table) give the
+    same pre-final-exponentiation bytes as the oracle, including pairs with points at infinity."""
+    import paritytech_bn_b200 as bn
+    n = 200
+    g1, g2 = util.points_cpu(util.scalars(n, stream=61), util.scalars(n, stream=62))
+    g1 = g1.reshape(n, G1).copy(); g2 = g2.reshape(n, G2).copy()
+    g1[5] = util.G1_INF; g2[9] = util.G2_INF; g1[199] = util.G1_INF; g2[199] = util.G2_INF
+    g1, g2 = g1.reshape(-1), g2.reshape(-1)
+    exp, exp_ok = c.miller_loop_many(g2, g1)
+    got, ok = eng.miller_loop_many(g2, g1)
+    assert got.tobytes() == exp.tobytes() and (ok == exp_ok).all()
+    os.environ["BN254_FUSED_MILLER"] = "1"
+    try:
+        e2 = bn.Engine(0)
+    finally:
+        del os.environ["BN254_FUSED_MILLER"]
+    got2, ok2 = e2.miller_loop_many(g2, g1)
+    e2.close()
+    assert got2.tobytes() == exp.tobytes() and (ok2 == exp_ok).all()
+
+
+def test_miller_product_and_distributed_protocol_single_process(eng):
+    """bn254_miller_product + the gather/combine protocol of paritytech_bn_b200.distributed, run in one
+    process over 3 ragged shards (the gloo world_size-2 test covers the process-group plumbing)."""
+    import paritytech_bn_b200 as bn
+    n = 11
+    g1, g2 = util.points_cpu(util.scalars(n, stream=71), util.scalars(n, stream=72))
+    g1 = g1.reshape(n, G1).copy(); g1[4] = util.G1_INF; g1 = g1.reshape(-1)
+    assert eng.gt_one().tobytes() == util.GT_ONE.tobytes()
+    assert eng.miller_product(g1, g2).tobytes() == c.miller_loop_batch_skip(g2, g1).tobytes()
+    parts = []
+    for d in range(3):
+        lo, hi = bn.shard_range(n, d, 3)
+        parts.append(eng.miller_product(g1[lo * G1:hi * G1], g2[lo * G2:hi * G2]))
+    out, is_one = bn.combine_partials(eng, np.stack(parts))
+    assert out.tobytes() == c.pairing_batch(g1, g2).tobytes() and not is_one
+    out1, _ = eng.pairing_batch(g1, g2)
+    assert out1.tobytes() == out.tobytes()
+
+
+def test_pairing_full_batch_round_trip_properties(eng):
+    """2^16 pairings (BASELINE config #2 size) through size-independent properties: bilinearity in the first
+    argument e(2P, Q) == e(P, Q)^2 for every pair, no result equals one, and a 256-element sample bit-exact."""
+    n = int(os.environ.get("BN_TEST_FULL_PAIRINGS", str(1 << 16)))
+    fr1, fr2 = util.fr_bytes(util.scalars(n, stream=81)), util.fr_bytes(util.scalars(n, stream=82))
+    g1 = eng.g1_mul(np.tile(util.G1_GEN, n), fr1)
+    g2 = eng.g2_mul(np.tile(util.G2_GEN, n), fr2)
+    two = util.fr_bytes([2] * n)
+    g1x2 = eng.g1_mul(g1, two)
+    e1 = eng.pairing(g1, g2)
+    e2 = eng.pairing(g1x2, g2)
+    assert e2.tobytes() == eng.gt_mul(e1, e1).tobytes()
+    assert not (e1.reshape(n, GT) == util.GT_ONE).all(axis=1).any()
+    idx = np.arange(0, n, max(1, n // 256))[:256]
+    s1 = g1.reshape(n, G1)[idx].reshape(-1); s2 = g2.reshape(n, G2)[idx].reshape(-1)
+    assert e1.reshape(n, GT)[idx].tobytes() == c.pairing_many(s1, s2).tobytes()
