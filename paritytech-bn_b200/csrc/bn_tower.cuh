@@ -351,14 +351,25 @@ BN_HD_NOINLINE void fq12_cyclotomic_sqr(Fq12& r, const Fq12& a) {
     cpv(r.c1.c0, z2); cpv(r.c1.c1, z1); cpv(r.c1.c2, z5);
 }
 // conj(a^u), u = 4965661367192848881 (63 bits); value of src/fields/fq12.rs:121-124 + :249-266.
-// (The reference's multiply-by-one on the first set bit is skipped: same value.)
+// The reference runs plain square-and-multiply (62 squarings, 28 multiplications incl. one by 1).  a lies in
+// the cyclotomic subgroup here (a^-1 = conj(a) is free), so the same power is reached with the width-3 signed
+// window recoding u = sum d_i 2^i, d_i in {0, +-1, +-3}: 62 squarings, 17 multiplications + 2 for a^3.
+// Bit i of NZ: d_i != 0; of NEG: d_i < 0; of M3: |d_i| = 3 (generated and checked against u by tools/gen_constants.py).
+#define BN_U_WNAF3_NZ 0x4908924444891211ull
+#define BN_U_WNAF3_NEG 0x0108000400880210ull
+#define BN_U_WNAF3_M3 0x0108804404880200ull
 BN_HD_NOINLINE void fq12_exp_by_neg_z(Fq12& r, const Fq12& a) {
-    const uint64_t u = ((uint64_t)BN_U_HI << 32) | BN_U_LO;
-    Fq12 acc;  // bit 62
-    cpv(acc, a);
+    Fq12 a3, t, acc;
+    fq12_cyclotomic_sqr(t, a);
+    fq12_mul(a3, t, a);
+    cpv(acc, a);                                   // top digit (bit 62) is +1
     for (int i = 61; i >= 0; i--) {
         fq12_cyclotomic_sqr(acc, acc);
-        if ((u >> i) & 1) fq12_mul(acc, acc, a);
+        if ((BN_U_WNAF3_NZ >> i) & 1) {
+            const Fq12& m = ((BN_U_WNAF3_M3 >> i) & 1) ? a3 : a;
+            if ((BN_U_WNAF3_NEG >> i) & 1) { fq12_conj(t, m); fq12_mul(acc, acc, t); }
+            else fq12_mul(acc, acc, m);
+        }
     }
     fq12_conj(r, acc);
 }

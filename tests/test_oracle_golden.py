@@ -136,3 +136,18 @@ def test_g2_subgroup_and_group_law():
     b = o.g_mul(o.FQ_OPS, o.G1_ONE, 54321)
     assert o.g_eq(o.FQ_OPS, o.g_add(o.FQ_OPS, a, b), o.g_mul(o.FQ_OPS, o.G1_ONE, 66666))
     assert o.g_is_zero(o.FQ_OPS, o.g_add(o.FQ_OPS, o.g_mul(o.FQ_OPS, o.G1_ONE, o.R_ORDER - 1), o.G1_ONE))
+
+
+def test_wnaf3_recoding_of_u_in_device_header():
+    """The width-3 signed-window digits of u used by fq12_exp_by_neg_z (bn_tower.cuh) reconstruct u."""
+    import os
+    import re
+    src = open(os.path.join(os.path.dirname(__file__), "..", "paritytech-bn_b200", "csrc", "bn_tower.cuh")).read()
+    m = {k: int(re.search(r"#define BN_U_WNAF3_%s (0x[0-9a-f]+)ull" % k, src).group(1), 16) for k in ("NZ", "NEG", "M3")}
+    v = 0
+    for i in range(64):
+        if (m["NZ"] >> i) & 1:
+            d = 3 if (m["M3"] >> i) & 1 else 1
+            v += (-d if (m["NEG"] >> i) & 1 else d) << i
+    assert v == 4965661367192848881                      # src/fields/fq12.rs:122
+    assert m["NEG"] & ~m["NZ"] == 0 and m["M3"] & ~m["NZ"] == 0 and (m["NZ"] >> 62) == 1 and not (m["NEG"] >> 62) & 1
