@@ -13,6 +13,18 @@ namespace bn {
 #define BN_MIN_BLOCKS 8
 #endif
 #define BN_KERNEL __global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS)
+// the final exponentiation has no state besides Fq12 values in local memory: 96 registers (10 blocks/SM) cost no
+// spills and give 5 warps per sub-partition on batches > 2^16 (+5 %, profiles/r01_bench_history.md)
+#ifndef BN_MIN_BLOCKS_FEXP
+#define BN_MIN_BLOCKS_FEXP 10
+#endif
+#define BN_KERNEL_FEXP __global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS_FEXP)
+#ifndef BN_MIN_BLOCKS_LINES
+#define BN_MIN_BLOCKS_LINES BN_MIN_BLOCKS
+#endif
+#ifndef BN_MIN_BLOCKS_MTAB
+#define BN_MIN_BLOCKS_MTAB BN_MIN_BLOCKS
+#endif
 
 __device__ __forceinline__ size_t gtid() { return (size_t)blockIdx.x * blockDim.x + threadIdx.x; }
 
@@ -65,7 +77,7 @@ BN_KERNEL k_miller_many(const G2* __restrict__ q, const G1* __restrict__ p, Fq12
     if (ok) ok[i] = good ? 1 : 0;
 }
 
-BN_KERNEL k_final_exp_many(const Fq12* __restrict__ in, Fq12* __restrict__ out, uint8_t* __restrict__ some,
+BN_KERNEL_FEXP k_final_exp_many(const Fq12* __restrict__ in, Fq12* __restrict__ out, uint8_t* __restrict__ some,
                            uint8_t* __restrict__ is_one, size_t n) {
     size_t i = gtid();
     if (i >= n) return;
@@ -89,7 +101,7 @@ BN_KERNEL k_final_exp_easy(const Fq12* __restrict__ in, Fq12* __restrict__ out, 
     out[i] = r;
     some[i] = s ? 1 : 0;
 }
-BN_KERNEL k_final_exp_hard(const Fq12* __restrict__ in, const uint8_t* __restrict__ some_in, Fq12* __restrict__ out,
+BN_KERNEL_FEXP k_final_exp_hard(const Fq12* __restrict__ in, const uint8_t* __restrict__ some_in, Fq12* __restrict__ out,
                            uint8_t* __restrict__ some, uint8_t* __restrict__ is_one, size_t n) {
     size_t i = gtid();
     if (i >= n) return;
@@ -243,7 +255,7 @@ BN_KERNEL k_g2_precompute(const G2* __restrict__ q, uint4* __restrict__ tab, Aff
     g2_walk_lines(qa, s);
 }
 
-BN_KERNEL k_g2_lines_affine(const AffG2* __restrict__ qa, const uint8_t* __restrict__ ok, uint4* __restrict__ tab, size_t n) {
+__global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS_LINES) k_g2_lines_affine(const AffG2* __restrict__ qa, const uint8_t* __restrict__ ok, uint4* __restrict__ tab, size_t n) {
     size_t i = gtid();
     if (i >= n || !ok[i]) return;
     AffG2 q = qa[i];
@@ -251,7 +263,7 @@ BN_KERNEL k_g2_lines_affine(const AffG2* __restrict__ qa, const uint8_t* __restr
     s.tab = tab; s.n_tables = n; s.j = i; s.idx = 0;
     g2_walk_lines(q, s);
 }
-BN_KERNEL k_miller_table_affine(const AffG1* __restrict__ pa_in, const uint8_t* __restrict__ ok_in, const uint4* __restrict__ tab,
+__global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS_MTAB) k_miller_table_affine(const AffG1* __restrict__ pa_in, const uint8_t* __restrict__ ok_in, const uint4* __restrict__ tab,
                                 Fq12* __restrict__ f_out, uint8_t* __restrict__ ok_out, size_t n) {
     size_t i = gtid();
     if (i >= n) return;
