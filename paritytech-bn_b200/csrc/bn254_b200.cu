@@ -196,7 +196,7 @@ static int miller_many_dev(bn254_ctx* ctx, const G2* d_g2, const G1* d_g1, Fq12*
     for (size_t lo = 0; lo < n; lo += chunk) {
         size_t m = n - lo < chunk ? n - lo : chunk;
         LAUNCH(ctx, k_pairs_to_affine, m, d_g2 + lo, d_g1 + lo, qa, pa, ok, m);
-        LAUNCH(ctx, k_g2_lines_affine, m, (const AffG2*)qa, (const uint8_t*)ok, tab, m);
+        LAUNCH(ctx, k_g2_lines_affine, m, (const AffG2*)qa, (const uint8_t*)ok, tab, m, (size_t)1);
         LAUNCH(ctx, k_miller_table_affine, m, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tab, d_f + lo, d_ok ? d_ok + lo : (uint8_t*)nullptr, m);
     }
     return 0;
@@ -248,7 +248,7 @@ int bn254_pairing_many_dev_timed(bn254_ctx* ctx, const void* d_g1, const void* d
                 CU(cudaEventRecord(ev[0], ctx->stream));
                 LAUNCH(ctx, k_pairs_to_affine, m, g2 + lo, g1 + lo, qa, pa, ok, m);
                 CU(cudaEventRecord(ev[1], ctx->stream));
-                LAUNCH(ctx, k_g2_lines_affine, m, (const AffG2*)qa, (const uint8_t*)ok, tab, m);
+                LAUNCH(ctx, k_g2_lines_affine, m, (const AffG2*)qa, (const uint8_t*)ok, tab, m, (size_t)1);
                 CU(cudaEventRecord(ev[2], ctx->stream));
                 LAUNCH(ctx, k_miller_table_affine, m, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tab, f + lo, (uint8_t*)nullptr, m);
                 CU(cudaEventRecord(ev[3], ctx->stream));
@@ -326,20 +326,53 @@ static int miller_products_dev(bn254_ctx* ctx, const G1* d_g1v, const G2* d_g2v,
     size_t m = pc ? pc->n : 0;
     const uint4* tab = pc ? pc->tab : nullptr;
     if (m > 8) return fail(BN254_ERR_ARG, "at most 8 shared tables per check");
-    if (v <= 1 && m <= 4) {
-        LAUNCH(ctx, (k_miller_product<1, 4>), n_checks, d_g1v, d_g2v, (int)v, d_g1s, tab, (int)m, d_f, n_checks);
-    } else if (v <= 4 && m <= 4) {
-        LAUNCH(ctx, (k_miller_product<4, 4>), n_checks, d_g1v, d_g2v, (int)v, d_g1s, tab, (int)m, d_f, n_checks);
-    } else if (v <= 8) {
-        LAUNCH(ctx, (k_miller_product<8, 8>), n_checks, d_g1v, d_g2v, (int)v, d_g1s, tab, (int)m, d_f, n_checks);
-    } else {
+    if (v > 8) {
         // many pairs per check: independent Miller loops, then a per-check product (same field element)
         if (m != 0) return fail(BN254_ERR_ARG, "more than 8 variable pairs cannot be combined with shared tables");
         DevBuf tmp;
         TRY(tmp.alloc(n_checks * v * sizeof(Fq12)));
-        LAUNCH(ctx, k_miller_many, n_checks * v, d_g2v, d_g1v, tmp.as<Fq12>(), (uint8_t*)nullptr, n_checks * v);
+        TRY(miller_many_dev(ctx, d_g2v, d_g1v, tmp.as<Fq12>(), (uint8_t*)nullptr, n_checks * v));
         LAUNCH(ctx, k_fq12_group_product, n_checks, (const Fq12*)tmp.as<Fq12>(), v, d_f, n_checks);
         CU(cudaStreamSynchronize(ctx->stream));   // tmp is freed on return
+        return 0;
+    }
+    if (!ctx->split_miller || v == 0) {
+        // single kernel: line coefficients of the variable G2 points produced on the fly
+        if (v <= 1 && m <= 4) {
+            LAUNCH(ctx, (k_miller_product<1, 4>), n_checks, d_g1v, d_g2v, (int)v, d_g1s, tab, (int)m, d_f, n_checks);
+        } else if (v <= 4 && m <= 4) {
+            LAUNCH(ctx, (k_miller_product<4, 4>), n_checks, d_g1v, d_g2v, (int)v, d_g1s, tab, (int)m, d_f, n_checks);
+        } else {
+            LAUNCH(ctx, (k_miller_product<8, 8>), n_checks, d_g1v, d_g2v, (int)v, d_g1s, tab, (int)m, d_f, n_checks);
+        }
+        return 0;
+    }
+    // split path: affine conversion and line tables of the variable pairs (slot layout of table_slot), then one
+    // product kernel per chunk of checks reading per-check and shared tables
+    size_t chunk = MILLER_CHUNK / v;
+    if (chunk > n_checks) chunk = n_checks;
+    size_t pairs = chunk * v;
+    size_t tab_bytes = (size_t)BN254_N_COEFFS * 12 * pairs * sizeof(uint4);
+    size_t qa_off = tab_bytes, pa_off = qa_off + pairs * sizeof(AffG2), ok_off = pa_off + pairs * sizeof(AffG1);
+    void* ws = nullptr;
+    TRY(ctx_workspace(ctx, ok_off + ((pairs + 15) & ~(size_t)15), &ws));
+    uint4* tabv = (uint4*)ws;
+    AffG2* qa = (AffG2*)((char*)ws + qa_off);
+    AffG1* pa = (AffG1*)((char*)ws + pa_off);
+    uint8_t* ok = (uint8_t*)ws + ok_off;
+    for (size_t lo = 0; lo < n_checks; lo += chunk) {
+        size_t nc = n_checks - lo < chunk ? n_checks - lo : chunk;
+        size_t np = nc * v;
+        LAUNCH(ctx, k_pairs_to_affine, np, d_g2v + lo * v, d_g1v + lo * v, qa, pa, ok, np);
+        LAUNCH(ctx, k_g2_lines_affine, np, (const AffG2*)qa, (const uint8_t*)ok, tabv, np, v);
+        const G1* gs = d_g1s ? d_g1s + lo * m : nullptr;
+        if (v <= 1 && m <= 4) {
+            LAUNCH(ctx, (k_miller_product_tables<1, 4>), nc, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
+        } else if (v <= 4 && m <= 4) {
+            LAUNCH(ctx, (k_miller_product_tables<4, 4>), nc, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
+        } else {
+            LAUNCH(ctx, (k_miller_product_tables<8, 8>), nc, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
+        }
     }
     return 0;
 }

@@ -255,13 +255,49 @@ BN_KERNEL k_g2_precompute(const G2* __restrict__ q, uint4* __restrict__ tab, Aff
     g2_walk_lines(qa, s);
 }
 
-__global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS_LINES) k_g2_lines_affine(const AffG2* __restrict__ qa, const uint8_t* __restrict__ ok, uint4* __restrict__ tab, size_t n) {
+// Table slot of pair t: identity for independent pairings (v = 1); for product checks with v pairs per check
+// (pair t = check t/v, position t%v) the slot is (t%v)*n_checks + t/v, so that the threads of the product
+// kernel (one per check) read consecutive 16-byte words for every position.
+__device__ __forceinline__ size_t table_slot(size_t t, size_t v, size_t n) { return v <= 1 ? t : (t % v) * (n / v) + t / v; }
+__global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS_LINES) k_g2_lines_affine(const AffG2* __restrict__ qa, const uint8_t* __restrict__ ok,
+                                                                                  uint4* __restrict__ tab, size_t n, size_t v) {
     size_t i = gtid();
     if (i >= n || !ok[i]) return;
     AffG2 q = qa[i];
     TableSink s;
-    s.tab = tab; s.n_tables = n; s.j = i; s.idx = 0;
+    s.tab = tab; s.n_tables = n; s.j = table_slot(i, v, n); s.idx = 0;
     g2_walk_lines(q, s);
+}
+// Product checks from line tables: one thread per check, shared squaring chain (groups::miller_loop_batch,
+// src/groups/mod.rs:609-640).  Variable pairs: affine P / ok flags / per-pair tables from the two kernels above
+// (slot layout of table_slot); shared pairs: Jacobian G1 points against the shared G2Precomp tables (broadcast loads).
+template <int MAXV, int MAXS>
+BN_KERNEL k_miller_product_tables(const AffG1* __restrict__ pa, const uint8_t* __restrict__ ok, const uint4* __restrict__ tabv, int v,
+                                  const G1* __restrict__ g1s, const uint4* __restrict__ tabs, int m,
+                                  Fq12* __restrict__ f_out, size_t n_checks) {
+    size_t i = gtid();
+    if (i >= n_checks) return;
+    AffG1 P[MAXV];
+    AffG1 PS[MAXS];
+    int jv[MAXV], js[MAXS];
+    int nv = 0, ns = 0;
+    for (int j = 0; j < v; j++)          // skip semantics of pairing_batch, src/groups/mod.rs:909-920
+        if (ok[i * v + j]) { P[nv] = pa[i * v + j]; jv[nv++] = j; }
+    for (int j = 0; j < m; j++) {
+        G1 pp = g1s[i * m + j];
+        if (jac_to_affine(PS[ns], pp)) js[ns++] = j;
+    }
+    Fq12 f = fq12_one();
+    EllCoeffs c;
+    size_t nt = n_checks * (size_t)v;
+    bool started = false;
+#pragma unroll 1
+    for (int idx = 0; idx < BN_N_COEFFS; idx++) {
+        if (started && coeff_is_doubling(idx)) fq12_sqr(f, f);
+        for (int j = 0; j < nv; j++) { load_coeff(c, tabv, nt, (size_t)jv[j] * n_checks + i, idx); line_mul(f, c, P[j]); started = true; }
+        for (int j = 0; j < ns; j++) { load_coeff(c, tabs, m, js[j], idx); line_mul(f, c, PS[j]); started = true; }
+    }
+    f_out[i] = f;
 }
 __global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS_MTAB) k_miller_table_affine(const AffG1* __restrict__ pa_in, const uint8_t* __restrict__ ok_in, const uint4* __restrict__ tab,
                                 Fq12* __restrict__ f_out, uint8_t* __restrict__ ok_out, size_t n) {

@@ -237,6 +237,12 @@ BN_HD uint32_t naf_digit(int k) {
     return (w >> (2 * (k & 15))) & 3u;
 }
 #define BN_N_COEFFS 87
+// bit c set <=> coefficient triple c of G2Precomp.coeffs comes from a doubling step (64 of the 87; the Miller
+// loop squares f before each of them).  Derived from the NAF table above; checked by
+// tests/test_oracle_golden.py::test_doubling_mask_matches_naf.
+#define BN_DBL_MASK_LO 0xb7b7ddbbf76dededull
+#define BN_DBL_MASK_HI 0x00000000001db77bull
+BN_HD bool coeff_is_doubling(int c) { return (((c < 64) ? (BN_DBL_MASK_LO >> c) : (BN_DBL_MASK_HI >> (c - 64))) & 1ull) != 0; }
 
 // one line evaluated at P and multiplied into f: the call shape at src/groups/mod.rs:589
 BN_HD void line_mul(Fq12& f, const EllCoeffs& c, const AffG1& p) {

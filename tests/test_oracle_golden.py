@@ -151,3 +151,21 @@ def test_wnaf3_recoding_of_u_in_device_header():
             v += (-d if (m["NEG"] >> i) & 1 else d) << i
     assert v == 4965661367192848881                      # src/fields/fq12.rs:122
     assert m["NEG"] & ~m["NZ"] == 0 and m["M3"] & ~m["NZ"] == 0 and (m["NZ"] >> 62) == 1 and not (m["NEG"] >> 62) & 1
+
+
+def test_doubling_mask_matches_naf():
+    """BN_DBL_MASK_* in bn_curve.cuh marks exactly the doubling-step coefficients of precompute()'s 87 triples."""
+    import os
+    import re
+    from oracle import bn254_ref as o
+    src = open(os.path.join(os.path.dirname(__file__), "..", "paritytech-bn_b200", "csrc", "bn_curve.cuh")).read()
+    lo = int(re.search(r"#define BN_DBL_MASK_LO (0x[0-9a-f]+)ull", src).group(1), 16)
+    hi = int(re.search(r"#define BN_DBL_MASK_HI (0x[0-9a-f]+)ull", src).group(1), 16)
+    bits = []
+    for d in o.ATE_LOOP_COUNT_NAF:
+        bits.append(1)
+        if d != 0:
+            bits.append(0)
+    bits += [0, 0]
+    assert len(bits) == 87
+    assert lo | (hi << 64) == sum(b << i for i, b in enumerate(bits))
