@@ -140,12 +140,16 @@ class Engine:
         return self.lib.bn254_build_info().decode()
 
     # ---- pairing surface (host buffers) ----------------------------------------------------------
-    def pairing(self, g1, g2):
-        """n x pairing(p, q) -> n x Gt (src/lib.rs:611-613)."""
+    def pairing(self, g1, g2, out=None):
+        """n x pairing(p, q) -> n x Gt (src/lib.rs:611-613).  `out`: optional caller-owned uint8 buffer of
+        n*384 bytes (e.g. pinned memory) to receive the result."""
         g1, n = _arr(g1, G1_BYTES)
         g2, n2 = _arr(g2, G2_BYTES)
         assert n == n2
-        out = np.empty(n * GT_BYTES, dtype=np.uint8)
+        if out is None:
+            out = np.empty(n * GT_BYTES, dtype=np.uint8)
+        else:
+            assert out.dtype == np.uint8 and out.size == n * GT_BYTES and out.flags["C_CONTIGUOUS"]
         self._check(self.lib.bn254_pairing_many(self.ctx, _p(g1), _p(g2), _p(out), ctypes.c_size_t(n)))
         return out
 
