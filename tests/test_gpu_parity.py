@@ -348,3 +348,26 @@ def test_pairing_full_batch_round_trip_properties(eng):
     idx = np.arange(0, n, max(1, n // 256))[:256]
     s1 = g1.reshape(n, G1)[idx].reshape(-1); s2 = g2.reshape(n, G2)[idx].reshape(-1)
     assert e1.reshape(n, GT)[idx].tobytes() == c.pairing_many(s1, s2).tobytes()
+
+
+def test_pairing_across_table_chunk_boundary(eng):
+    """The split Miller path materialises line tables for at most 2^17 pairings at a time: a batch of 2^17 + 37
+    pairs crosses the chunk boundary with a ragged tail; indices around the boundary and the tail are compared
+    with the oracle bit for bit, and the second chunk must not depend on the first (same pairs, same bytes)."""
+    n = (1 << 17) + 37
+    base = 4096
+    fr1, fr2 = util.fr_bytes(util.scalars(base, stream=85)), util.fr_bytes(util.scalars(base, stream=86))
+    p1 = eng.g1_mul(np.tile(util.G1_GEN, base), fr1).reshape(base, G1)
+    p2 = eng.g2_mul(np.tile(util.G2_GEN, base), fr2).reshape(base, G2)
+    idx = (np.arange(n) * 2654435761 % base).astype(np.int64)       # a fixed pseudo-random arrangement of the 4096 pairs
+    g1 = p1[idx].reshape(-1); g2 = p2[(idx * 7 + 3) % base].reshape(-1)
+    out = eng.pairing(g1, g2).reshape(n, GT)
+    sel = np.concatenate([np.arange(0, 8), np.arange((1 << 17) - 8, (1 << 17) + 8), np.arange(n - 8, n)])
+    exp = c.pairing_many(g1.reshape(n, G1)[sel].reshape(-1), g2.reshape(n, G2)[sel].reshape(-1))
+    assert out[sel].tobytes() == exp.tobytes()
+    # identical pairs give identical bytes wherever they sit in the batch
+    key = idx * base + (idx * 7 + 3) % base
+    order = np.argsort(key, kind="stable")
+    same = key[order][1:] == key[order][:-1]
+    a, b = order[1:][same][:2000], order[:-1][same][:2000]
+    assert (out[a] == out[b]).all()
