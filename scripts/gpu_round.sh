@@ -1,5 +1,5 @@
 #!/bin/bash
-# one GPU visit: smoke, parity tests, bench, launch list, one ncu --set full capture of the two pairing kernels
+# one GPU visit: smoke, parity tests, bench (+reference arm), launch list, one ncu --set full capture of the pairing kernels
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
 nproc > gpurun_out/nproc.txt
@@ -9,6 +9,5 @@ timeout 600 python bench.py --steps 5 --warmup 3 > gpurun_out/bench_default.json
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err
 timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/plain_bench.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
-timeout 300 python scripts/profile_pairing.py 16 2 > gpurun_out/plain_prof.log 2>&1 &&
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:'k_miller_many|k_final_exp_many' -s 2 -c 2 -o gpurun_out/prof_pairing -f python scripts/profile_pairing.py 16 2 > gpurun_out/ncu_full.log 2>&1
-tail -c 400 gpurun_out/smoke.log; tail -5 gpurun_out/pytest_gpu.log; cut -c1-2500 gpurun_out/bench_default.json; tail -3 gpurun_out/bench_default.err; cat gpurun_out/bench_reference.json | cut -c1-600; tail -3 gpurun_out/ncu_full.log; ls -la gpurun_out
+bash scripts/gpu_profile.sh
+tail -c 300 gpurun_out/smoke.log; tail -3 gpurun_out/pytest_gpu.log; cut -c1-400 gpurun_out/bench_default.json; tail -2 gpurun_out/bench_default.err; cut -c1-300 gpurun_out/bench_reference.json
