@@ -119,6 +119,15 @@ int bn254_g2_mul_many_dev(bn254_ctx* ctx, const void* d_g2, const void* d_fr, vo
 int bn254_g1_normalize_many(bn254_ctx* ctx, const void* g1, void* g1_out, size_t n);
 int bn254_g2_normalize_many(bn254_ctx* ctx, const void* g2, void* g2_out, size_t n);
 
+/* ---- AffineG1::new / AffineG2::new: src/lib.rs:437-447, :639-649 -> src/groups/mod.rs:94-113 ---- */
+/* xy: n affine points (x, y) as Montgomery images (64 B for G1, 128 B for G2).  status[i] = 0 Ok,
+ * 1 GroupError::NotOnCurve, 2 GroupError::NotInSubgroup (G2 only: p * (-1) + p != 0). */
+#define BN254_AFFINE_OK 0
+#define BN254_AFFINE_NOT_ON_CURVE 1
+#define BN254_AFFINE_NOT_IN_SUBGROUP 2
+int bn254_g1_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n);
+int bn254_g2_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n);
+
 /* ---- shared G2Precomp: src/groups/mod.rs:573-577, :701-728 ------------------------------------- */
 /* Precompute the 87 line-coefficient triples of n G2 points once; the tables stay on the device.
  * Returns BN254_ERR_TO_AFFINE if a point is at infinity. */

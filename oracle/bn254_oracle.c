@@ -766,6 +766,181 @@ void orc_g2_mul_many(const void *p, const void *fr, void *out, size_t n, int thr
         ST(g2, out, i, g2_mul(LD(g2, p, i), &k));
     }
 }
+/* AffineG::new, src/groups/mod.rs:94-113: 0 = Ok, 1 = Err(NotOnCurve), 2 = Err(NotInSubgroup).  Input: affine (x, y)
+ * Montgomery images.  G1Params::check_order() is false (:401), G2Params::check_order() is true (:469-471). */
+void orc_g1_affine_check_many(const void *xy, uint8_t *status, size_t n) {
+    orc_init();
+    fq b = fq_from_u64(3);
+    for (size_t i = 0; i < n; i++) {
+        fq x = LD(fq, xy, 2 * i), y = LD(fq, xy, 2 * i + 1);
+        status[i] = fq_eq(fq_sqr(y), fq_add(fq_mul(fq_sqr(x), x), b)) ? 0 : 1;
+    }
+}
+void orc_g2_affine_check_many(const void *xy, uint8_t *status, size_t n, int threads) {
+    orc_init();
+    threads = clamp_threads(threads);
+    u256 rm1 = FR.m;
+    rm1.l[0] -= 1;                       /* r - 1 = canonical value of -Fr::one(); r is odd, no borrow */
+#pragma omp parallel for num_threads(threads) schedule(static)
+    for (size_t i = 0; i < n; i++) {
+        fq2 x = LD(fq2, xy, 2 * i), y = LD(fq2, xy, 2 * i + 1);
+        if (!fq2_eq(fq2_sqr(y), fq2_add(fq2_mul(fq2_sqr(x), x), G2_B))) { status[i] = 1; continue; }
+        g2 p;
+        p.x = x; p.y = y; p.z = FQ2_ONE;
+        g2 t = g2_add(g2_mul(p, &rm1), p);
+        status[i] = fq2_is_zero(t.z) ? 0 : 2;
+    }
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* square roots and the compressed wire formats                                   */
+/* ------------------------------------------------------------------------------------------ */
+static u256 fq_canonical(fq a) {               /* From<Fq> for U256, src/fields/fp.rs:13-20: one Montgomery mul by 1 */
+    u256 one = {{1, 0}};
+    u256_mont_mul(&a, &one, &FQ.m, FQ.inv);
+    return a;
+}
+static u256 fq_minus3_div4(void) {             /* src/fields/fp.rs:233-236: (-3) * 4^-1 = (q-3)/4 since q = 3 mod 4 */
+    u256 e = FQ.m, three = {{3, 0}};
+    sub_noborrow(&e, &three); div2(&e); div2(&e);
+    return e;
+}
+static u256 fq_minus1_div2(void) {             /* src/fields/fp.rs:238-241: (q-1)/2 */
+    u256 e = FQ.m, one = {{1, 0}};
+    sub_noborrow(&e, &one); div2(&e);
+    return e;
+}
+static int fq_sqrt(fq a, fq *out) {            /* Fq::sqrt, src/fields/fp.rs:245-260 */
+    u256 e = fq_minus3_div4();
+    fq a1 = fq_pow_u256(a, &e);
+    fq a1a = fq_mul(a1, a);
+    fq a0 = fq_mul(a1, a1a);
+    if (fq_eq(a0, fq_neg(FQ.one))) return 0;
+    *out = a1a;
+    return 1;
+}
+static int fq2_sqrt(fq2 a, fq2 *out) {         /* Fq2::sqrt, src/fields/fq2.rs:208-224 */
+    u256 e34 = fq_minus3_div4(), e12 = fq_minus1_div2();
+    fq2 a1 = fq2_pow_u256(a, &e34);
+    fq2 a1a = fq2_mul(a1, a);
+    fq2 alpha = fq2_mul(a1, a1a);
+    fq2 a0 = fq2_mul(fq2_pow_u256(alpha, &FQ.m), alpha);
+    fq2 m1 = fq2_neg(FQ2_ONE);
+    if (fq2_eq(a0, m1)) return 0;
+    if (fq2_eq(alpha, m1)) {
+        fq2 i = {FQ_ZERO, FQ.one};
+        *out = fq2_mul(i, a1a);
+    } else {
+        fq2 b = fq2_pow_u256(fq2_add(alpha, FQ2_ONE), &e12);
+        *out = fq2_mul(b, a1a);
+    }
+    return 1;
+}
+static u128 be128(const uint8_t *s) { u128 v = 0; for (int i = 0; i < 16; i++) v = (v << 8) | s[i]; return v; }
+/* U512::from_slice + divrem, src/arith.rs:82-138: bit-serial long division of the 512-bit big-endian value by q.
+ * Returns 0 when the quotient does not fit below q (the reference's `None`). */
+static int u512_divrem_q(const uint8_t s[64], u256 *quot, u256 *rem) {
+    u128 n[4];                                  /* n[3] most significant, :92-95 */
+    for (int l = 3, i = 0; l >= 0; l--, i += 16) n[l] = be128(s + i);
+    u256 q = {{0, 0}}, r = {{0, 0}};
+    int q_some = 1;
+    for (int i = 511; i >= 0; i--) {
+        r.l[1] = (r.l[1] << 1) | (r.l[0] >> 127);   /* mul2; the modulus' two top bits are clear */
+        r.l[0] = (r.l[0] << 1) | ((n[i >> 7] >> (i & 127)) & 1);
+        if (u256_cmp(&r, &FQ.m) >= 0) {
+            sub_noborrow(&r, &FQ.m);
+            if (i >= 256) q_some = 0; else q.l[i >> 7] |= (u128)1 << (i & 127);
+        }
+    }
+    *rem = r;
+    if (!q_some || u256_cmp(&q, &FQ.m) >= 0) return 0;
+    *quot = q;
+    return 1;
+}
+static fq fq_from_u256(u256 a) { u256_mont_mul(&a, &FQ.r2, &FQ.m, FQ.inv); return a; }   /* Fq::new for a < q */
+
+/* G1::from_compressed, src/lib.rs:359-375.  in: n x 33 bytes.  out: n x G1 (z = one), zero-filled on error.
+ * status: 0 Ok, 1 CurveError::InvalidEncoding, 2 CurveError::NotMember, 3 CurveError::Field(NotMember).
+ * The checks run in the reference's order: field membership, square root, tag, AffineG1::new. */
+void orc_g1_from_compressed_many(const uint8_t *in, void *out, uint8_t *status, size_t n) {
+    orc_init();
+    fq b = fq_from_u64(3);
+    for (size_t i = 0; i < n; i++) {
+        const uint8_t *s = in + 33 * i;
+        g1 res;
+        memset(&res, 0, sizeof res);
+        uint8_t st = 0;
+        u256 xv = {{be128(s + 17), be128(s + 1)}};          /* U256::from_slice: big-endian */
+        if (u256_cmp(&xv, &FQ.m) >= 0) st = 3;
+        else {
+            fq x = fq_from_u256(xv), y;
+            fq y2 = fq_add(fq_mul(fq_mul(x, x), x), b);
+            if (!fq_sqrt(y2, &y)) st = 2;
+            else {
+                int odd = (int)(fq_canonical(y).l[0] & 1);
+                if (s[0] == 2) { if (odd) y = fq_neg(y); }
+                else if (s[0] == 3) { if (!odd) y = fq_neg(y); }
+                else st = 1;
+                if (!st) {
+                    if (!fq_eq(fq_sqr(y), fq_add(fq_mul(fq_sqr(x), x), b))) st = 2;
+                    else { res.x = x; res.y = y; res.z = FQ.one; }
+                }
+            }
+        }
+        status[i] = st;
+        ST(g1, out, i, res);
+    }
+}
+/* G2::from_compressed, src/lib.rs:506-526 (Fq2::from_slice :260-267, to_u512 src/fields/fq2.rs:226-231). */
+void orc_g2_from_compressed_many(const uint8_t *in, void *out, uint8_t *status, size_t n, int threads) {
+    orc_init();
+    threads = clamp_threads(threads);
+    u256 rm1 = FR.m;
+    rm1.l[0] -= 1;
+#pragma omp parallel for num_threads(threads) schedule(dynamic, 1)
+    for (size_t i = 0; i < n; i++) {
+        const uint8_t *s = in + 65 * i;
+        g2 res;
+        memset(&res, 0, sizeof res);
+        uint8_t st = 0;
+        u256 c1, c0;
+        if (!u512_divrem_q(s + 1, &c1, &c0)) st = 3;
+        else {
+            fq2 x = {fq_from_u256(c0), fq_from_u256(c1)}, y;
+            fq2 y2 = fq2_add(fq2_mul(fq2_mul(x, x), x), G2_B);
+            if (!fq2_sqrt(y2, &y)) st = 2;
+            else {
+                fq2 yn = fq2_neg(y);
+                u256 a1 = fq_canonical(y.c1), a0 = fq_canonical(y.c0), b1 = fq_canonical(yn.c1), b0 = fq_canonical(yn.c0);
+                int c = u256_cmp(&a1, &b1);     /* c1 * q + c0 compares lexicographically on (c1, c0) */
+                int y_gt = c > 0 || (c == 0 && u256_cmp(&a0, &b0) > 0);
+                fq2 e_y = y;
+                if (s[0] == 10) e_y = y_gt ? yn : y;
+                else if (s[0] == 11) e_y = y_gt ? y : yn;
+                else st = 1;
+                if (!st) {
+                    if (!fq2_eq(fq2_sqr(e_y), fq2_add(fq2_mul(fq2_sqr(x), x), G2_B))) st = 2;
+                    else {
+                        g2 p;
+                        p.x = x; p.y = e_y; p.z = FQ2_ONE;
+                        g2 t = g2_add(g2_mul(p, &rm1), p);
+                        if (!fq2_is_zero(t.z)) st = 2; else res = p;
+                    }
+                }
+            }
+        }
+        status[i] = st;
+        ST(g2, out, i, res);
+    }
+}
+void orc_fq_sqrt_many(const void *a, void *out, uint8_t *some, size_t n) {
+    orc_init();
+    for (size_t i = 0; i < n; i++) { fq r = FQ_ZERO; some[i] = (uint8_t)fq_sqrt(LD(fq, a, i), &r); ST(fq, out, i, r); }
+}
+void orc_fq2_sqrt_many(const void *a, void *out, uint8_t *some, size_t n) {
+    orc_init();
+    for (size_t i = 0; i < n; i++) { fq2 r = FQ2_ZERO; some[i] = (uint8_t)fq2_sqrt(LD(fq2, a, i), &r); ST(fq2, out, i, r); }
+}
 void orc_g1_add_many(const void *a, const void *b, void *out, size_t n) { orc_init(); for (size_t i = 0; i < n; i++) ST(g1, out, i, g1_add(LD(g1, a, i), LD(g1, b, i))); }
 void orc_g2_add_many(const void *a, const void *b, void *out, size_t n) { orc_init(); for (size_t i = 0; i < n; i++) ST(g2, out, i, g2_add(LD(g2, a, i), LD(g2, b, i))); }
 void orc_g1_double_many(const void *a, void *out, size_t n) { orc_init(); for (size_t i = 0; i < n; i++) ST(g1, out, i, g1_double(LD(g1, a, i))); }

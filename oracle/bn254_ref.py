@@ -571,6 +571,92 @@ def g2_in_subgroup(x, y):
 
 
 # ---------------------------------------------------------------------------------------------
+# Square roots and the compressed wire formats
+# ---------------------------------------------------------------------------------------------
+FQ_MINUS3_DIV4 = (Q - 3) // 4   # (-3) * 4^-1 mod q, src/fields/fp.rs:233-236 (q = 3 mod 4, so this is exact)
+FQ_MINUS1_DIV2 = (Q - 1) // 2   # (-1) * 2^-1 mod q, src/fields/fp.rs:238-241
+
+
+def fq_sqrt(a):
+    """Fq::sqrt, src/fields/fp.rs:245-260: a1 = a^((q-3)/4); None iff a1 * (a1 * a) == -1; else a1 * a."""
+    a1 = pow(a, FQ_MINUS3_DIV4, Q)
+    a1a = a1 * a % Q
+    if a1 * a1a % Q == Q - 1:
+        return None
+    return a1a
+
+
+def fq2_sqrt(a):
+    """Fq2::sqrt, src/fields/fq2.rs:208-224 (the q = 3 mod 4 'complex method')."""
+    a1 = fq2_pow(a, FQ_MINUS3_DIV4)
+    a1a = fq2_mul(a1, a)
+    alpha = fq2_mul(a1, a1a)
+    a0 = fq2_mul(fq2_pow(alpha, Q), alpha)
+    minus_one = (Q - 1, 0)
+    if a0 == minus_one:
+        return None
+    if alpha == minus_one:
+        return fq2_mul((0, 1), a1a)
+    b = fq2_pow(fq2_add(alpha, FQ2_ONE), FQ_MINUS1_DIV2)
+    return fq2_mul(b, a1a)
+
+
+# status codes shared with include/bn254_b200.h (BN254_DECODE_*)
+DECODE_OK, DECODE_INVALID_ENCODING, DECODE_NOT_MEMBER, DECODE_FIELD_NOT_MEMBER = 0, 1, 2, 3
+
+
+def g1_from_compressed(b):
+    """G1::from_compressed, src/lib.rs:359-375 -> (status, (x, y, 1) | None).  33 bytes: tag 2/3, x big-endian.
+    The order of the checks is the reference's: field membership, square root, tag, AffineG1::new."""
+    if len(b) != 33:
+        return DECODE_INVALID_ENCODING, None
+    sign, x = b[0], int.from_bytes(b[1:], "big")
+    if x >= Q:                                   # Fq::from_slice -> CurveError::Field(NotMember), :154-159
+        return DECODE_FIELD_NOT_MEMBER, None
+    y = fq_sqrt((x * x * x + G1_B) % Q)
+    if y is None:
+        return DECODE_NOT_MEMBER, None
+    if sign == 2:
+        if y & 1:
+            y = (-y) % Q
+    elif sign == 3:
+        if not y & 1:
+            y = (-y) % Q
+    else:
+        return DECODE_INVALID_ENCODING, None
+    if not affine_on_curve(FQ_OPS, G1_B, x, y):
+        return DECODE_NOT_MEMBER, None
+    return DECODE_OK, (x, y, 1)
+
+
+def g2_from_compressed(b):
+    """G2::from_compressed, src/lib.rs:506-526.  65 bytes: tag 10/11, then x as the 512-bit big-endian
+    integer c1 * q + c0 (Fq2::from_slice :260-267 via U512::divrem, src/arith.rs:116-138).  y is the root
+    with the smaller (tag 10) or larger (tag 11) value of c1 * q + c0 (to_u512, src/fields/fq2.rs:226-231)."""
+    if len(b) != 65:
+        return DECODE_INVALID_ENCODING, None
+    sign, n = b[0], int.from_bytes(b[1:], "big")
+    c1, c0 = divmod(n, Q)
+    if c1 >= Q:                                  # quotient None or >= modulus -> Field(NotMember)
+        return DECODE_FIELD_NOT_MEMBER, None
+    x = (c0, c1)
+    y = fq2_sqrt(fq2_add(fq2_mul(fq2_mul(x, x), x), G2_B))
+    if y is None:
+        return DECODE_NOT_MEMBER, None
+    yn = fq2_neg(y)
+    y_gt = y[1] * Q + y[0] > yn[1] * Q + yn[0]
+    if sign == 10:
+        e_y = yn if y_gt else y
+    elif sign == 11:
+        e_y = y if y_gt else yn
+    else:
+        return DECODE_INVALID_ENCODING, None
+    if not affine_on_curve(FQ2_OPS, G2_B, x, e_y) or not g2_in_subgroup(x, e_y):
+        return DECODE_NOT_MEMBER, None
+    return DECODE_OK, (x, e_y, FQ2_ONE)
+
+
+# ---------------------------------------------------------------------------------------------
 # Pairing (src/groups/mod.rs:515-926)
 # ---------------------------------------------------------------------------------------------
 

@@ -215,6 +215,48 @@ def miller_loop_many(q, p, threads=0):
     return out, ok
 
 
+def g1_affine_check(xy):
+    """AffineG1::new status per (x, y): 0 Ok, 1 NotOnCurve (src/groups/mod.rs:94-113; no order check for G1)."""
+    xy, n = _in(xy, 2 * FQ)
+    st = np.empty(n, dtype=np.uint8)
+    lib().orc_g1_affine_check_many(_p(xy), _p(st), ctypes.c_size_t(n))
+    return st
+
+
+def g2_affine_check(xy, threads=0):
+    """AffineG2::new status per (x, y): 0 Ok, 1 NotOnCurve, 2 NotInSubgroup (src/groups/mod.rs:94-113)."""
+    xy, n = _in(xy, 4 * FQ)
+    st = np.empty(n, dtype=np.uint8)
+    lib().orc_g2_affine_check_many(_p(xy), _p(st), ctypes.c_size_t(n), ctypes.c_int(threads))
+    return st
+
+
+def _raw(a, unit):
+    a = np.ascontiguousarray(np.frombuffer(bytes(a), dtype=np.uint8) if isinstance(a, (bytes, bytearray)) else a, dtype=np.uint8).reshape(-1)
+    assert a.size % unit == 0
+    return a, a.size // unit
+
+
+def g1_from_compressed(enc):
+    """G1::from_compressed per 33-byte record (src/lib.rs:359-375) -> (G1 images, status)."""
+    enc, n = _raw(enc, 33)
+    out, st = np.empty(n * G1, dtype=np.uint8), np.empty(n, dtype=np.uint8)
+    lib().orc_g1_from_compressed_many(_p(enc), _p(out), _p(st), ctypes.c_size_t(n))
+    return out, st
+
+
+def g2_from_compressed(enc, threads=0):
+    """G2::from_compressed per 65-byte record (src/lib.rs:506-526) -> (G2 images, status)."""
+    enc, n = _raw(enc, 65)
+    out, st = np.empty(n * G2, dtype=np.uint8), np.empty(n, dtype=np.uint8)
+    lib().orc_g2_from_compressed_many(_p(enc), _p(out), _p(st), ctypes.c_size_t(n), ctypes.c_int(threads))
+    return out, st
+
+
+fq_sqrt = _with_some("orc_fq_sqrt_many", FQ)
+fq2_sqrt = _with_some("orc_fq2_sqrt_many", 2 * FQ)
+
+
 def miller_loop_batch_skip(q, p):
     """Un-exponentiated Miller product with pairing_batch's skip semantics (pairs with a point at infinity
     contribute one; empty -> one): product of the single Miller values, src/groups/mod.rs:609-640."""

@@ -269,6 +269,20 @@ class Engine:
         self._check(self.lib.bn254_g2_normalize_many(self.ctx, _p(g2), _p(out), ctypes.c_size_t(n)))
         return out
 
+    def g1_affine_check(self, xy):
+        """AffineG1::new per (x, y) pair of Fq images: 0 Ok, 1 NotOnCurve (src/groups/mod.rs:94-113)."""
+        xy, n = _arr(xy, 2 * FQ_BYTES)
+        st = np.empty(n, dtype=np.uint8)
+        self._check(self.lib.bn254_g1_affine_check_many(self.ctx, _p(xy), _p(st), ctypes.c_size_t(n)))
+        return st
+
+    def g2_affine_check(self, xy):
+        """AffineG2::new per (x, y) pair of Fq2 images: 0 Ok, 1 NotOnCurve, 2 NotInSubgroup."""
+        xy, n = _arr(xy, 4 * FQ_BYTES)
+        st = np.empty(n, dtype=np.uint8)
+        self._check(self.lib.bn254_g2_affine_check_many(self.ctx, _p(xy), _p(st), ctypes.c_size_t(n)))
+        return st
+
     # ---- shared G2Precomp -------------------------------------------------------------------------
     def g2_precompute(self, g2):
         g2, n = _arr(g2, G2_BYTES)

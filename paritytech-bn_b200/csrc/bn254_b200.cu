@@ -599,6 +599,30 @@ int bn254_g2_normalize_many(bn254_ctx* ctx, const void* g2, void* out, size_t n)
     return 0;
 }
 
+static int affine_check_host(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n, bool g2) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!xy || !status) return fail(BN254_ERR_ARG, "null pointer");
+    size_t sz[2] = {n * (g2 ? sizeof(AffG2) : sizeof(AffG1)), n};
+    void* d[2];
+    TRY(ctx_io(ctx, sz, 2, d));
+    TRY(h2d(ctx, d[0], xy, sz[0]));
+    if (g2) {
+        LAUNCH(ctx, (k_affine_check<Fq2Ops, G2Check>), n, (const AffG2*)d[0], (uint8_t*)d[1], n);
+    } else {
+        LAUNCH(ctx, (k_affine_check<FqOps, G1Check>), n, (const AffG1*)d[0], (uint8_t*)d[1], n);
+    }
+    TRY(d2h(ctx, status, d[1], n));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int bn254_g1_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n) {
+    return affine_check_host(ctx, xy, status, n, false);
+}
+int bn254_g2_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n) {
+    return affine_check_host(ctx, xy, status, n, true);
+}
+
 // ---------------------------------------------------------------------------------------------
 // shared G2Precomp tables
 // ---------------------------------------------------------------------------------------------

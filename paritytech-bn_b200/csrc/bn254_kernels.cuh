@@ -400,6 +400,38 @@ BN_KERNEL k_jac_normalize(const Jac<F>* __restrict__ p, Jac<F>* __restrict__ out
     out[i] = r;
 }
 
+// AffineG::new (src/groups/mod.rs:94-113), SURVEY 8f N2: status 0 = Ok, 1 = NotOnCurve, 2 = NotInSubgroup.
+// G1 has no order check (G1Params::check_order() == false, :401); G2 multiplies by r - 1 = -Fr::one() and adds p
+// (:103), i.e. one full 254-bit G2 scalar multiplication per deserialised point -- the same k_jac_mul body.
+struct G1Check { static BN_HD Fq coeff_b() { Fq b = BN_C_G1_B; return b; } static constexpr bool check_order = false; };
+struct G2Check { static BN_HD Fq2 coeff_b() { Fq2 b = BN_C_G2_B; return b; } static constexpr bool check_order = true; };
+template <class F, class C>
+BN_KERNEL k_affine_check(const Aff<F>* __restrict__ pts, uint8_t* __restrict__ status, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Aff<F> a = pts[i];
+    typename F::T lhs, rhs, b = C::coeff_b();
+    F::sqr(lhs, a.y);
+    F::sqr(rhs, a.x);
+    F::mul(rhs, rhs, a.x);
+    F::add(rhs, rhs, b);
+    uint8_t st = 0;
+    if (!F::eq(lhs, rhs)) st = 1;
+    else if (C::check_order) {
+        const uint32_t rl[8] = BN_R_LIMBS;
+        uint32_t k[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) k[j] = rl[j];
+        k[0] -= 1u;                                  // r - 1 (r is odd: no borrow)
+        Jac<F> p, t;
+        p.x = a.x; p.y = a.y; p.z = F::one();
+        jac_mul(t, p, k);
+        jac_add(t, t, p);
+        if (!F::is_zero(t.z)) st = 2;
+    }
+    status[i] = st;
+}
+
 // field-level test hook (bn254_field_op_many)
 BN_KERNEL k_field_op(int op, const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ out, size_t n) {
     size_t i = gtid();

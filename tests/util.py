@@ -120,3 +120,65 @@ def groth16_checks(n_checks, stream=7, scalar_mul=None):
         "g2_var": np.ascontiguousarray(g2_flat[:, 0]).reshape(-1),
         "valid": np.array(valid, dtype=np.uint8),
     }
+
+
+# ---------------------------------------------------------------------------------------------
+# SURVEY 8f N2/N3 inputs: affine points for AffineG::new and compressed encodings for from_compressed
+# ---------------------------------------------------------------------------------------------
+def affine_of(jac_images, unit):
+    """(x, y) Montgomery images of normalised Jacobian images (z = one); unit = 96 (G1) or 192 (G2)."""
+    a = np.asarray(jac_images, dtype=np.uint8).reshape(-1, unit)
+    return a[:, : 2 * unit // 3].reshape(-1).copy()
+
+
+def _rand_fq(rng):
+    return int.from_bytes(rng.bytes(40), "little") % Q
+
+
+def g2_curve_points_outside_subgroup(n, seed=11):
+    """n affine points of the twist E'(Fq2) found by solving y^2 = x^3 + b' for random x.  The group has order
+    r * (2q - r), so such a point lies in the r-torsion only with probability ~2^-254: AffineG2::new must
+    answer NotInSubgroup.  Canonical ((x0, x1), (y0, y1)) tuples."""
+    from oracle import bn254_ref as o
+    rng = np.random.default_rng(seed)
+    out = []
+    while len(out) < n:
+        x = (_rand_fq(rng), _rand_fq(rng))
+        y = o.fq2_sqrt(o.fq2_add(o.fq2_mul(o.fq2_sqr(x), x), o.G2_B))
+        if y is not None:
+            out.append((x, y))
+    return out
+
+
+def g2_small_order_points(n, seed=12):
+    """Points of E'(Fq2) with no r-torsion component: r * P for curve points P (order divides the cofactor
+    2q - r).  The hardest negatives for any shortcut subgroup test."""
+    from oracle import bn254_ref as o
+    out = []
+    for x, y in g2_curve_points_outside_subgroup(n, seed):
+        t = o.g_to_affine(o.FQ2_OPS, o.g_mul(o.FQ2_OPS, (x, y, o.FQ2_ONE), o.R_ORDER))
+        if t is not None:
+            out.append(t)
+    return out
+
+
+def affine_bytes(points):
+    """Montgomery images of canonical affine tuples: ints for G1 coordinates, pairs for G2 coordinates."""
+    flat = []
+    for x, y in points:
+        for c in (x, y):
+            flat.extend(c if isinstance(c, tuple) else (c,))
+    return np.frombuffer(fq_mont_bytes(flat), dtype=np.uint8).copy()
+
+
+def compress_g1(x, y):
+    """Inverse of G1::from_compressed (src/lib.rs:359-375): tag 2 for even canonical y, 3 for odd, x big-endian."""
+    return bytes([3 if y & 1 else 2]) + x.to_bytes(32, "big")
+
+
+def compress_g2(x, y):
+    """Inverse of G2::from_compressed (src/lib.rs:506-526): tag 10 when y is the smaller of (y, -y) as the
+    integer c1 * q + c0, else 11; x as the 512-bit big-endian integer c1 * q + c0."""
+    yn = ((-y[0]) % Q, (-y[1]) % Q)
+    gt = y[1] * Q + y[0] > yn[1] * Q + yn[0]
+    return bytes([11 if gt else 10]) + (x[1] * Q + x[0]).to_bytes(64, "big")
