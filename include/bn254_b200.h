@@ -128,6 +128,20 @@ int bn254_g2_normalize_many(bn254_ctx* ctx, const void* g2, void* g2_out, size_t
 int bn254_g1_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n);
 int bn254_g2_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n);
 
+/* ---- G1::from_compressed src/lib.rs:359-375, G2::from_compressed :506-526 ---- */
+/* enc: n records of 33 bytes (G1: tag 2/3, x big-endian) or 65 bytes (G2: tag 10/11, x = c1*q + c0 as a
+ * 512-bit big-endian integer).  out: n Jacobian images with z = one (all-zero bytes for a failed record).
+ * status[i] = the reference's Result: 0 Ok, 1 CurveError::InvalidEncoding (tag), 2 CurveError::NotMember
+ * (no square root, or AffineG::new refused the point), 3 CurveError::Field(FieldError::NotMember) (x >= q).
+ * The checks run in the reference's order: field, square root, tag, AffineG::new.  The length check of the
+ * slice (:360, :508) is the caller's: the record size is fixed by this ABI. */
+#define BN254_DECODE_OK 0
+#define BN254_DECODE_INVALID_ENCODING 1
+#define BN254_DECODE_NOT_MEMBER 2
+#define BN254_DECODE_FIELD_NOT_MEMBER 3
+int bn254_g1_from_compressed_many(bn254_ctx* ctx, const uint8_t* enc, void* g1_out, uint8_t* status, size_t n);
+int bn254_g2_from_compressed_many(bn254_ctx* ctx, const uint8_t* enc, void* g2_out, uint8_t* status, size_t n);
+
 /* ---- shared G2Precomp: src/groups/mod.rs:573-577, :701-728 ------------------------------------- */
 /* Precompute the 87 line-coefficient triples of n G2 points once; the tables stay on the device.
  * Returns BN254_ERR_TO_AFFINE if a point is at infinity. */

@@ -283,6 +283,24 @@ class Engine:
         self._check(self.lib.bn254_g2_affine_check_many(self.ctx, _p(xy), _p(st), ctypes.c_size_t(n)))
         return st
 
+    def _from_compressed(self, fn, enc, rec, unit):
+        enc = np.ascontiguousarray(np.frombuffer(bytes(enc), dtype=np.uint8) if isinstance(enc, (bytes, bytearray)) else enc,
+                                   dtype=np.uint8).reshape(-1)
+        if enc.size % rec:
+            raise ValueError("encoding length is not a multiple of %d bytes" % rec)
+        n = enc.size // rec
+        out, st = np.empty(n * unit, dtype=np.uint8), np.empty(n, dtype=np.uint8)
+        self._check(fn(self.ctx, _p(enc), _p(out), _p(st), ctypes.c_size_t(n)))
+        return out, st
+
+    def g1_from_compressed(self, enc):
+        """G1::from_compressed per 33-byte record (src/lib.rs:359-375) -> (G1 images, status bytes)."""
+        return self._from_compressed(self.lib.bn254_g1_from_compressed_many, enc, 33, G1_BYTES)
+
+    def g2_from_compressed(self, enc):
+        """G2::from_compressed per 65-byte record (src/lib.rs:506-526) -> (G2 images, status bytes)."""
+        return self._from_compressed(self.lib.bn254_g2_from_compressed_many, enc, 65, G2_BYTES)
+
     # ---- shared G2Precomp -------------------------------------------------------------------------
     def g2_precompute(self, g2):
         g2, n = _arr(g2, G2_BYTES)

@@ -608,9 +608,9 @@ static int affine_check_host(bn254_ctx* ctx, const void* xy, uint8_t* status, si
     TRY(ctx_io(ctx, sz, 2, d));
     TRY(h2d(ctx, d[0], xy, sz[0]));
     if (g2) {
-        LAUNCH(ctx, (k_affine_check<Fq2Ops, G2Check>), n, (const AffG2*)d[0], (uint8_t*)d[1], n);
+        LAUNCH(ctx, k_g2_affine_check, n, (const AffG2*)d[0], (uint8_t*)d[1], n);
     } else {
-        LAUNCH(ctx, (k_affine_check<FqOps, G1Check>), n, (const AffG1*)d[0], (uint8_t*)d[1], n);
+        LAUNCH(ctx, k_g1_affine_check, n, (const AffG1*)d[0], (uint8_t*)d[1], n);
     }
     TRY(d2h(ctx, status, d[1], n));
     CU(cudaStreamSynchronize(ctx->stream));
@@ -621,6 +621,31 @@ int bn254_g1_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, 
 }
 int bn254_g2_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n) {
     return affine_check_host(ctx, xy, status, n, true);
+}
+
+static int from_compressed_host(bn254_ctx* ctx, const uint8_t* enc, void* out, uint8_t* status, size_t n, bool g2) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!enc || !out || !status) return fail(BN254_ERR_ARG, "null pointer");
+    size_t sz[3] = {n * (g2 ? 65 : 33), n * (g2 ? sizeof(G2) : sizeof(G1)), n};
+    void* d[3];
+    TRY(ctx_io(ctx, sz, 3, d));
+    TRY(h2d(ctx, d[0], enc, sz[0]));
+    if (g2) {
+        LAUNCH(ctx, k_g2_from_compressed, n, (const uint8_t*)d[0], (G2*)d[1], (uint8_t*)d[2], n);
+    } else {
+        LAUNCH(ctx, k_g1_from_compressed, n, (const uint8_t*)d[0], (G1*)d[1], (uint8_t*)d[2], n);
+    }
+    TRY(d2h(ctx, out, d[1], sz[1]));
+    TRY(d2h(ctx, status, d[2], n));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+int bn254_g1_from_compressed_many(bn254_ctx* ctx, const uint8_t* enc, void* g1_out, uint8_t* status, size_t n) {
+    return from_compressed_host(ctx, enc, g1_out, status, n, false);
+}
+int bn254_g2_from_compressed_many(bn254_ctx* ctx, const uint8_t* enc, void* g2_out, uint8_t* status, size_t n) {
+    return from_compressed_host(ctx, enc, g2_out, status, n, true);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -3,6 +3,7 @@
 // register-blocked around the IMAD.WIDE carry chains of fq_ptx.cuh.  See DESIGN.md for the layout.
 #pragma once
 #include "bn_curve.cuh"
+#include "bn_wire.cuh"
 
 namespace bn {
 
@@ -402,33 +403,41 @@ BN_KERNEL k_jac_normalize(const Jac<F>* __restrict__ p, Jac<F>* __restrict__ out
 
 // AffineG::new (src/groups/mod.rs:94-113), SURVEY 8f N2: status 0 = Ok, 1 = NotOnCurve, 2 = NotInSubgroup.
 // G1 has no order check (G1Params::check_order() == false, :401); G2 multiplies by r - 1 = -Fr::one() and adds p
-// (:103), i.e. one full 254-bit G2 scalar multiplication per deserialised point -- the same k_jac_mul body.
-struct G1Check { static BN_HD Fq coeff_b() { Fq b = BN_C_G1_B; return b; } static constexpr bool check_order = false; };
-struct G2Check { static BN_HD Fq2 coeff_b() { Fq2 b = BN_C_G2_B; return b; } static constexpr bool check_order = true; };
-template <class F, class C>
-BN_KERNEL k_affine_check(const Aff<F>* __restrict__ pts, uint8_t* __restrict__ status, size_t n) {
+// (:103), i.e. one full 254-bit G2 scalar multiplication per deserialised point.
+BN_KERNEL k_g1_affine_check(const AffG1* __restrict__ pts, uint8_t* __restrict__ status, size_t n) {
     size_t i = gtid();
     if (i >= n) return;
-    Aff<F> a = pts[i];
-    typename F::T lhs, rhs, b = C::coeff_b();
-    F::sqr(lhs, a.y);
-    F::sqr(rhs, a.x);
-    F::mul(rhs, rhs, a.x);
-    F::add(rhs, rhs, b);
-    uint8_t st = 0;
-    if (!F::eq(lhs, rhs)) st = 1;
-    else if (C::check_order) {
-        const uint32_t rl[8] = BN_R_LIMBS;
-        uint32_t k[8];
-#pragma unroll
-        for (int j = 0; j < 8; j++) k[j] = rl[j];
-        k[0] -= 1u;                                  // r - 1 (r is odd: no borrow)
-        Jac<F> p, t;
-        p.x = a.x; p.y = a.y; p.z = F::one();
-        jac_mul(t, p, k);
-        jac_add(t, t, p);
-        if (!F::is_zero(t.z)) st = 2;
-    }
+    AffG1 a = pts[i];
+    status[i] = g1_affine_status(a);
+}
+BN_KERNEL k_g2_affine_check(const AffG2* __restrict__ pts, uint8_t* __restrict__ status, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    AffG2 a = pts[i];
+    status[i] = g2_affine_status(a);
+}
+// G1::from_compressed / G2::from_compressed (src/lib.rs:359-375, :506-526), SURVEY 8f N3.  33 / 65 bytes per
+// record; a failed record writes an all-zero image and its CurveError as the status byte.
+BN_KERNEL k_g1_from_compressed(const uint8_t* __restrict__ enc, G1* __restrict__ out, uint8_t* __restrict__ status, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    uint8_t rec[33];
+    for (int j = 0; j < 33; j++) rec[j] = enc[i * 33 + j];
+    G1 g;
+    uint8_t st = g1_decode(g, rec);
+    if (st != 0) { g.x = fq_zero(); g.y = fq_zero(); g.z = fq_zero(); }
+    out[i] = g;
+    status[i] = st;
+}
+BN_KERNEL k_g2_from_compressed(const uint8_t* __restrict__ enc, G2* __restrict__ out, uint8_t* __restrict__ status, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    uint8_t rec[65];
+    for (int j = 0; j < 65; j++) rec[j] = enc[i * 65 + j];
+    G2 g;
+    uint8_t st = g2_decode(g, rec);
+    if (st != 0) { g.x = fq2_zero(); g.y = fq2_zero(); g.z = fq2_zero(); }
+    out[i] = g;
     status[i] = st;
 }
 

@@ -1,10 +1,11 @@
-// TEST-ONLY host build of the device headers (bn_fq/bn_tower/bn_curve .cuh) with the portable
+// TEST-ONLY host build of the device headers (bn_fq/bn_tower/bn_curve/bn_wire .cuh) with the portable
 // arithmetic back end.  Lets the CPU test-suite check every formula, constant and control path
 // of the CUDA code against the oracle without a GPU.  Never linked into the shipped library.
 #include <stddef.h>
 #include <string.h>
 #define BN_HOST_SIM 1
 #include "../../paritytech-bn_b200/csrc/bn_curve.cuh"
+#include "../../paritytech-bn_b200/csrc/bn_wire.cuh"
 using namespace bn;
 
 template <class T> static T ld(const void* p, size_t i) { T v; memcpy(&v, (const char*)p + i * sizeof(T), sizeof(T)); return v; }
@@ -90,4 +91,36 @@ extern "C" void hs_constants(void* o) {
 #define PUT(x) do { memcpy(p, &(x), sizeof(x)); p += sizeof(x); } while (0)
     PUT(one); PUT(r2); PUT(r3); PUT(two_inv); PUT(g1b); PUT(g1y); PUT(g2b); PUT(tx); PUT(ty);
     PUT(f61); PUT(f62); PUT(f12); PUT(gx); PUT(gy);
+}
+
+// validation, square roots, compressed wire formats (bn_wire.cuh)
+extern "C" void hs_g1_affine_check(const void* xy, unsigned char* status, size_t n) {
+    for (size_t i = 0; i < n; i++) status[i] = g1_affine_status(ld<AffG1>(xy, i));
+}
+extern "C" void hs_g2_affine_check(const void* xy, unsigned char* status, size_t n) {
+    for (size_t i = 0; i < n; i++) status[i] = g2_affine_status(ld<AffG2>(xy, i));
+}
+extern "C" void hs_fq_sqrt(const void* a, void* o, unsigned char* some, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r = fq_zero(); some[i] = fq_sqrt(r, x); st(o, i, r); }
+}
+extern "C" void hs_fq2_sqrt(const void* a, void* o, unsigned char* some, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq2 x = ld<Fq2>(a, i), r = fq2_zero(); some[i] = fq2_sqrt(r, x); st(o, i, r); }
+}
+extern "C" void hs_g1_from_compressed(const unsigned char* enc, void* o, unsigned char* status, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        G1 g; memset(&g, 0, sizeof g);
+        G1 t;
+        status[i] = g1_decode(t, enc + 33 * i);
+        if (status[i] == 0) g = t;
+        st(o, i, g);
+    }
+}
+extern "C" void hs_g2_from_compressed(const unsigned char* enc, void* o, unsigned char* status, size_t n) {
+    for (size_t i = 0; i < n; i++) {
+        G2 g; memset(&g, 0, sizeof g);
+        G2 t;
+        status[i] = g2_decode(t, enc + 65 * i);
+        if (status[i] == 0) g = t;
+        st(o, i, g);
+    }
 }

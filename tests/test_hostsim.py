@@ -186,3 +186,51 @@ def test_constants_match_reference_literals(golden):
             exp += [int(x) for x in m[tab][k]]
     exp += [int(x) for x in m["g2_one"]["x"]] + [int(x) for x in m["g2_one"]["y"]]
     assert vals[:len(exp)] == exp
+
+
+# ---- bn_wire.cuh against the oracles ----
+def test_wire_sqrt_and_validation_host_build():
+    from tests import util
+    from tests.test_wire_oracle import _mont
+    vals = [rng.randrange(o.Q) for _ in range(16)] + [0, 1, 4, o.Q - 1]
+    a = _mont(vals)
+    out, some = np.empty_like(a), np.empty(len(vals), dtype=np.uint8)
+    hostsim.lib().hs_fq_sqrt(_p(a), _p(out), _p(some), ctypes.c_size_t(len(vals)))
+    ro, so = c.fq_sqrt(a)
+    assert some.tobytes() == so.tobytes()
+    for i in range(len(vals)):
+        if some[i]:
+            assert out[32 * i:32 * i + 32].tobytes() == ro[32 * i:32 * i + 32].tobytes()
+    pairs = [(rng.randrange(o.Q), rng.randrange(o.Q)) for _ in range(8)] + [(0, 0), (4, 0), (0, 1), (o.Q - 1, 0), (o.Q - 4, 0), (1, 2)]
+    a = _mont([w for pr in pairs for w in pr])
+    out, some = np.empty_like(a), np.empty(len(pairs), dtype=np.uint8)
+    hostsim.lib().hs_fq2_sqrt(_p(a), _p(out), _p(some), ctypes.c_size_t(len(pairs)))
+    ro, so = c.fq2_sqrt(a)
+    assert some.tobytes() == so.tobytes()
+    for i in range(len(pairs)):
+        if some[i]:
+            assert out[64 * i:64 * i + 64].tobytes() == ro[64 * i:64 * i + 64].tobytes()
+    g1 = util.affine_bytes([(1, 2), (1, 1), (1, 3), (0, 0)])
+    st = np.empty(4, dtype=np.uint8)
+    hostsim.lib().hs_g1_affine_check(_p(g1), _p(st), ctypes.c_size_t(4))
+    assert list(st) == [0, 1, 1, 1]
+    gen = (o.G2_ONE[0], o.G2_ONE[1])
+    pts = [gen, ((1, 2), (3, 4))] + util.g2_curve_points_outside_subgroup(2) + util.g2_small_order_points(1)
+    g2 = util.affine_bytes(pts)
+    st = np.empty(len(pts), dtype=np.uint8)
+    hostsim.lib().hs_g2_affine_check(_p(g2), _p(st), ctypes.c_size_t(len(pts)))
+    assert st.tobytes() == c.g2_affine_check(g2).tobytes() and list(st) == [0, 1, 2, 2, 2]
+
+
+def test_wire_from_compressed_host_build():
+    from tests.test_wire_oracle import wire_cases_g1, wire_cases_g2
+    for cases, rec, unit, hs, ref in ((wire_cases_g1(), 33, G1, "hs_g1_from_compressed", c.g1_from_compressed),
+                                      (wire_cases_g2(), 65, G2, "hs_g2_from_compressed", c.g2_from_compressed)):
+        enc = np.frombuffer(b"".join(e for e, _ in cases), dtype=np.uint8).copy()
+        n = len(cases)
+        out, st = np.empty(n * unit, dtype=np.uint8), np.empty(n, dtype=np.uint8)
+        getattr(hostsim.lib(), hs)(_p(enc), _p(out), _p(st), ctypes.c_size_t(n))
+        ro, so = ref(enc)
+        assert st.tobytes() == so.tobytes()
+        assert out.tobytes() == ro.tobytes()
+        assert set(st) >= {0, 1, 2, 3}
