@@ -38,6 +38,7 @@ struct bn254_ctx {
     size_t ws_bytes;
     int split_miller;  // 1: three-kernel Miller path (default), 0: fused single kernel (BN254_FUSED_MILLER=1)
     int split_fexp;    // 1: easy + hard final-exponentiation kernels (BN254_SPLIT_FEXP=1), 0: one kernel
+    bool subgroup_ref; // true: G2 order check with the reference's [r-1]P + P ladder (BN254_SUBGROUP_REF=1); false: psi test
 };
 struct bn254_g2precomp {
     int device;
@@ -110,6 +111,7 @@ int bn254_ctx_create(int device, bn254_ctx** out) {
     c->io_bytes = 0;
     { const char* e = getenv("BN254_FUSED_MILLER"); c->split_miller = (e && e[0] == '1') ? 0 : 1; }
     { const char* e = getenv("BN254_SPLIT_FEXP"); c->split_fexp = (e && e[0] == '1') ? 1 : 0; }
+    { const char* e = getenv("BN254_SUBGROUP_REF"); c->subgroup_ref = (e && e[0] == '1'); }
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { delete c; return fail(BN254_ERR_CUDA, "cudaStreamCreate", e); }
     // deep call chains (Fq12 -> Fq6 -> Fq2 noinline bodies) need more than the default stack
@@ -608,7 +610,7 @@ static int affine_check_host(bn254_ctx* ctx, const void* xy, uint8_t* status, si
     TRY(ctx_io(ctx, sz, 2, d));
     TRY(h2d(ctx, d[0], xy, sz[0]));
     if (g2) {
-        LAUNCH(ctx, k_g2_affine_check, n, (const AffG2*)d[0], (uint8_t*)d[1], n);
+        LAUNCH(ctx, k_g2_affine_check, n, (const AffG2*)d[0], (uint8_t*)d[1], n, ctx->subgroup_ref);
     } else {
         LAUNCH(ctx, k_g1_affine_check, n, (const AffG1*)d[0], (uint8_t*)d[1], n);
     }
@@ -632,7 +634,7 @@ static int from_compressed_host(bn254_ctx* ctx, const uint8_t* enc, void* out, u
     TRY(ctx_io(ctx, sz, 3, d));
     TRY(h2d(ctx, d[0], enc, sz[0]));
     if (g2) {
-        LAUNCH(ctx, k_g2_from_compressed, n, (const uint8_t*)d[0], (G2*)d[1], (uint8_t*)d[2], n);
+        LAUNCH(ctx, k_g2_from_compressed, n, (const uint8_t*)d[0], (G2*)d[1], (uint8_t*)d[2], n, ctx->subgroup_ref);
     } else {
         LAUNCH(ctx, k_g1_from_compressed, n, (const uint8_t*)d[0], (G1*)d[1], (uint8_t*)d[2], n);
     }

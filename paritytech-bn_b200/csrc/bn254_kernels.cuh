@@ -410,11 +410,11 @@ BN_KERNEL k_g1_affine_check(const AffG1* __restrict__ pts, uint8_t* __restrict__
     AffG1 a = pts[i];
     status[i] = g1_affine_status(a);
 }
-BN_KERNEL k_g2_affine_check(const AffG2* __restrict__ pts, uint8_t* __restrict__ status, size_t n) {
+BN_KERNEL k_g2_affine_check(const AffG2* __restrict__ pts, uint8_t* __restrict__ status, size_t n, bool ref_ladder) {
     size_t i = gtid();
     if (i >= n) return;
     AffG2 a = pts[i];
-    status[i] = g2_affine_status(a);
+    status[i] = g2_affine_status(a, ref_ladder);
 }
 // G1::from_compressed / G2::from_compressed (src/lib.rs:359-375, :506-526), SURVEY 8f N3.  33 / 65 bytes per
 // record; a failed record writes an all-zero image and its CurveError as the status byte.
@@ -429,13 +429,14 @@ BN_KERNEL k_g1_from_compressed(const uint8_t* __restrict__ enc, G1* __restrict__
     out[i] = g;
     status[i] = st;
 }
-BN_KERNEL k_g2_from_compressed(const uint8_t* __restrict__ enc, G2* __restrict__ out, uint8_t* __restrict__ status, size_t n) {
+BN_KERNEL k_g2_from_compressed(const uint8_t* __restrict__ enc, G2* __restrict__ out, uint8_t* __restrict__ status, size_t n,
+                               bool ref_ladder) {
     size_t i = gtid();
     if (i >= n) return;
     uint8_t rec[65];
     for (int j = 0; j < 65; j++) rec[j] = enc[i * 65 + j];
     G2 g;
-    uint8_t st = g2_decode(g, rec);
+    uint8_t st = g2_decode(g, rec, ref_ladder);
     if (st != 0) { g.x = fq2_zero(); g.y = fq2_zero(); g.z = fq2_zero(); }
     out[i] = g;
     status[i] = st;

@@ -188,10 +188,43 @@ BN_HD_NOINLINE bool g2_in_subgroup_ref(const AffG2& a) {
     jac_add(t, t, p);
     return fq2_is_zero(t.z);
 }
+// The same predicate without the 254-bit ladder.  psi = twist^-1 . Frobenius . twist (AffineG2::mul_by_q, :694-699,
+// here on Jacobian triples: conjugate X, Y, Z and scale X, Y by the two twist constants) satisfies
+// psi^2 - t psi + q = 0 on all of E'(Fq2) and acts on the order-r subgroup as multiplication by q = 6u^2 mod r.
+// For BN curves  [u+1]P + psi([u]P) + psi^2([u]P) = psi^3([2u]P)  holds on that subgroup; conversely a point of
+// E'(Fq2) satisfying it is killed by the resultant of f(X) = -2uX^3 + uX^2 + uX + u + 1 and X^2 - tX + q, an
+// integer that r divides and that is coprime to the cofactor 2q - r (checked numerically in
+// tests/test_wire_oracle.py::test_fast_subgroup_test_is_exact), so its order divides r: the two predicates
+// agree on every on-curve input, including the small-order points of the cofactor.  One 63-bit ladder
+// instead of a 254-bit one.
+BN_HD void g2_psi(G2& r, const G2& p) {
+    const Fq2 cx = BN_C_TWIST_MUL_BY_Q_X, cy = BN_C_TWIST_MUL_BY_Q_Y;
+    Fq2 t;
+    fq2_conj(t, p.x); fq2_mul(r.x, t, cx);
+    fq2_conj(t, p.y); fq2_mul(r.y, t, cy);
+    fq2_conj(r.z, p.z);
+}
+BN_HD_NOINLINE bool g2_in_subgroup_psi(const AffG2& a) {
+    uint32_t k[8] = {BN_U_LO, BN_U_HI, 0u, 0u, 0u, 0u, 0u, 0u};
+    G2 p, up, b, c, d;
+    p.x = a.x; p.y = a.y; p.z = fq2_one();
+    jac_mul(up, p, k);                            // [u]P
+    g2_psi(b, up);                                // psi([u]P)
+    g2_psi(c, b);                                 // psi^2([u]P)
+    g2_psi(d, c);                                 // psi^3([u]P)
+    jac_add(up, up, p);                           // [u+1]P
+    jac_add(up, up, b);
+    jac_add(up, up, c);                           // left-hand side
+    jac_double(d, d);                             // psi^3([2u]P)
+    fq2_neg(up.y, up.y);
+    jac_add(d, d, up);
+    return fq2_is_zero(d.z);
+}
 BN_HD uint8_t g1_affine_status(const AffG1& a) { return g1_affine_on_curve(a) ? 0 : 1; }
-BN_HD uint8_t g2_affine_status(const AffG2& a) {
+BN_HD uint8_t g2_affine_status(const AffG2& a, bool ref_ladder) {
     if (!g2_affine_on_curve(a)) return 1;
-    return g2_in_subgroup_ref(a) ? 0 : 2;
+    bool in = ref_ladder ? g2_in_subgroup_ref(a) : g2_in_subgroup_psi(a);
+    return in ? 0 : 2;
 }
 
 // G1::from_compressed, src/lib.rs:359-375: checks in the reference's order (field, root, tag, AffineG1::new)
@@ -234,7 +267,7 @@ BN_HD bool fq2_u512_gt(const Fq2& a, const Fq2& b) {
     return limbs_cmp(x, y) > 0;
 }
 // G2::from_compressed, src/lib.rs:506-526
-BN_HD uint8_t g2_decode(G2& out, const uint8_t* s) {
+BN_HD uint8_t g2_decode(G2& out, const uint8_t* s, bool ref_ladder) {
     uint32_t c1[8], c0[8];
     if (!u512_divrem_q(c1, c0, s + 1)) return BN254_DECODE_FIELD_NOT_MEMBER_;
     AffG2 a;
@@ -250,7 +283,7 @@ BN_HD uint8_t g2_decode(G2& out, const uint8_t* s) {
     uint8_t tag = s[0];
     if (tag != 10 && tag != 11) return BN254_DECODE_INVALID_ENCODING_;
     a.y = ((tag == 10) == y_gt) ? yn : y;
-    uint8_t st = g2_affine_status(a);
+    uint8_t st = g2_affine_status(a, ref_ladder);
     if (st != 0) return BN254_DECODE_NOT_MEMBER_;
     out.x = a.x; out.y = a.y; out.z = fq2_one();
     return BN254_DECODE_OK_;

@@ -22,6 +22,7 @@ ap.add_argument("--g2-log2", type=int, default=16)
 ap.add_argument("--g1-log2", type=int, default=20)
 ap.add_argument("--reps", type=int, default=3)
 ap.add_argument("--cpu-sample", type=int, default=2048)
+ap.add_argument("--tag", default=os.environ.get("BN254_SUBGROUP_REF", "0") == "1" and "reference ladder" or "psi test")
 args = ap.parse_args()
 eng = bn.Engine(0)
 
@@ -55,7 +56,7 @@ def compress(g1, g2):
 
 def line(metric, n, t_gpu, cpu_n, t_cpu):
     print(json.dumps({"metric": metric, "value": n / t_gpu, "unit": "points/s", "n": n, "ms": t_gpu * 1e3,
-                      "timing": "wall clock around the C-ABI call, host buffers",
+                      "g2_order_check": args.tag, "timing": "wall clock around the C-ABI call, host buffers",
                       "cpu_baseline": {"value": cpu_n / t_cpu, "unit": "points/s", "cores": c.num_procs(), "kind": "port",
                                        "sample": "%d points" % cpu_n}}), flush=True)
 

@@ -97,8 +97,8 @@ extern "C" void hs_constants(void* o) {
 extern "C" void hs_g1_affine_check(const void* xy, unsigned char* status, size_t n) {
     for (size_t i = 0; i < n; i++) status[i] = g1_affine_status(ld<AffG1>(xy, i));
 }
-extern "C" void hs_g2_affine_check(const void* xy, unsigned char* status, size_t n) {
-    for (size_t i = 0; i < n; i++) status[i] = g2_affine_status(ld<AffG2>(xy, i));
+extern "C" void hs_g2_affine_check(const void* xy, unsigned char* status, size_t n, int ref_ladder) {
+    for (size_t i = 0; i < n; i++) status[i] = g2_affine_status(ld<AffG2>(xy, i), ref_ladder != 0);
 }
 extern "C" void hs_fq_sqrt(const void* a, void* o, unsigned char* some, size_t n) {
     for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r = fq_zero(); some[i] = fq_sqrt(r, x); st(o, i, r); }
@@ -115,11 +115,11 @@ extern "C" void hs_g1_from_compressed(const unsigned char* enc, void* o, unsigne
         st(o, i, g);
     }
 }
-extern "C" void hs_g2_from_compressed(const unsigned char* enc, void* o, unsigned char* status, size_t n) {
+extern "C" void hs_g2_from_compressed(const unsigned char* enc, void* o, unsigned char* status, size_t n, int ref_ladder) {
     for (size_t i = 0; i < n; i++) {
         G2 g; memset(&g, 0, sizeof g);
         G2 t;
-        status[i] = g2_decode(t, enc + 65 * i);
+        status[i] = g2_decode(t, enc + 65 * i, ref_ladder != 0);
         if (status[i] == 0) g = t;
         st(o, i, g);
     }

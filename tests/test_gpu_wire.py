@@ -99,3 +99,32 @@ def test_compress_decode_round_trip(eng):
     out, st = eng.g2_from_compressed(r2)
     ro, so = c.g2_from_compressed(r2)
     assert st.tobytes() == so.tobytes() and out.tobytes() == ro.tobytes() and set(st) == {2}
+
+
+def test_psi_subgroup_test_matches_reference_ladder(eng):
+    """The default 63-bit psi test and the reference's 254-bit [r-1]P + P ladder (BN254_SUBGROUP_REF=1) give the
+    same status on members, random curve points, cofactor-order points and off-curve points."""
+    import os
+    import paritytech_bn_b200 as bn
+    ks = util.scalars(500, stream=71) + [1, 2, o.BN_U, o.BN_U + 1, o.R_ORDER - 1]
+    g2 = c.g2_normalize(c.g2_mul(np.tile(util.G2_GEN, len(ks)), util.fr_bytes(ks)))
+    a2 = util.affine_of(g2, 192)
+    a2.reshape(-1, 128)[::7, 100] ^= 8
+    neg = util.affine_bytes(util.g2_curve_points_outside_subgroup(200, seed=72) + util.g2_small_order_points(40, seed=73))
+    a2 = np.concatenate([a2, neg])
+    fast = eng.g2_affine_check(a2)
+    os.environ["BN254_SUBGROUP_REF"] = "1"
+    try:
+        ref_eng = bn.Engine(0)
+    finally:
+        del os.environ["BN254_SUBGROUP_REF"]
+    try:
+        slow = ref_eng.g2_affine_check(a2)
+        enc = b"".join(e for e, _ in wire_cases_g2())
+        o1, s1 = eng.g2_from_compressed(enc)
+        o2, s2 = ref_eng.g2_from_compressed(enc)
+    finally:
+        ref_eng.close()
+    assert fast.tobytes() == slow.tobytes() == c.g2_affine_check(a2).tobytes()
+    assert set(fast[-240:]) == {2} and int((fast == 0).sum()) > 400
+    assert s1.tobytes() == s2.tobytes() and o1.tobytes() == o2.tobytes()

@@ -216,10 +216,12 @@ def test_wire_sqrt_and_validation_host_build():
     assert list(st) == [0, 1, 1, 1]
     gen = (o.G2_ONE[0], o.G2_ONE[1])
     pts = [gen, ((1, 2), (3, 4))] + util.g2_curve_points_outside_subgroup(2) + util.g2_small_order_points(1)
+    pts += [o.g_to_affine(o.FQ2_OPS, o.g_mul(o.FQ2_OPS, o.G2_ONE, k)) for k in (2, o.BN_U, o.R_ORDER - 1, o.BN_U + 1)]
     g2 = util.affine_bytes(pts)
-    st = np.empty(len(pts), dtype=np.uint8)
-    hostsim.lib().hs_g2_affine_check(_p(g2), _p(st), ctypes.c_size_t(len(pts)))
-    assert st.tobytes() == c.g2_affine_check(g2).tobytes() and list(st) == [0, 1, 2, 2, 2]
+    for ref_ladder in (0, 1):                     # psi test and the reference's [r-1]P + P ladder
+        st = np.empty(len(pts), dtype=np.uint8)
+        hostsim.lib().hs_g2_affine_check(_p(g2), _p(st), ctypes.c_size_t(len(pts)), ctypes.c_int(ref_ladder))
+        assert st.tobytes() == c.g2_affine_check(g2).tobytes() and list(st) == [0, 1, 2, 2, 2, 0, 0, 0, 0]
 
 
 def test_wire_from_compressed_host_build():
@@ -228,9 +230,10 @@ def test_wire_from_compressed_host_build():
                                       (wire_cases_g2(), 65, G2, "hs_g2_from_compressed", c.g2_from_compressed)):
         enc = np.frombuffer(b"".join(e for e, _ in cases), dtype=np.uint8).copy()
         n = len(cases)
-        out, st = np.empty(n * unit, dtype=np.uint8), np.empty(n, dtype=np.uint8)
-        getattr(hostsim.lib(), hs)(_p(enc), _p(out), _p(st), ctypes.c_size_t(n))
         ro, so = ref(enc)
-        assert st.tobytes() == so.tobytes()
-        assert out.tobytes() == ro.tobytes()
-        assert set(st) >= {0, 1, 2, 3}
+        for extra in ([[]] if unit == G1 else [[ctypes.c_int(0)], [ctypes.c_int(1)]]):
+            out, st = np.empty(n * unit, dtype=np.uint8), np.empty(n, dtype=np.uint8)
+            getattr(hostsim.lib(), hs)(_p(enc), _p(out), _p(st), ctypes.c_size_t(n), *extra)
+            assert st.tobytes() == so.tobytes()
+            assert out.tobytes() == ro.tobytes()
+            assert set(st) >= {0, 1, 2, 3}

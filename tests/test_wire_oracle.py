@@ -160,3 +160,24 @@ def test_from_compressed_c_vs_python_all_exits():
         assert s == st[i] and (want is None or s == want), (i, s, st[i], want)
         img = out[192 * i:192 * i + 192].tobytes()
         assert img == (util.fq_mont_bytes(list(g[0]) + list(g[1]) + [1, 0]) if s == 0 else bytes(192))
+
+
+def test_fast_subgroup_test_is_exact():
+    """The device's default G2 order check (bn_wire.cuh g2_in_subgroup_psi) replaces [r-1]P + P == 0 by
+    [u+1]P + psi([u]P) + psi^2([u]P) == psi^3([2u]P).  Exactness on all of E'(Fq2): psi satisfies
+    g(X) = X^2 - tX + q there, so a point passing the test is killed by Res(f, g) with
+    f(X) = -2uX^3 + uX^2 + uX + u + 1.  r divides that integer (the test holds on the subgroup) and it is
+    coprime to the cofactor 2q - r (nothing else passes)."""
+    from math import gcd
+    u, q, r = o.BN_U, o.Q, o.R_ORDER
+    t = 6 * u * u + 1
+    assert q + 1 - t == r
+    cof = 2 * q - r                               # #E'(Fq2) = r * (2q - r)
+    assert gcd(r, cof) == 1
+    # f mod g with X^2 = tX - q, X^3 = (t^2 - q)X - tq; Res(f, g) = c1^2 q + c0 c1 t + c0^2 for monic g
+    c1 = -2 * u * (t * t - q) + u * t + u
+    c0 = 2 * u * t * q - u * q + (u + 1)
+    res = c1 * c1 * q + c0 * c1 * t + c0 * c0
+    assert res % r == 0 and gcd(res, cof) == 1
+    lam = q % r                                   # psi acts on the subgroup as multiplication by q
+    assert (u + 1 + u * lam + u * lam * lam - 2 * u * pow(lam, 3, r)) % r == 0
