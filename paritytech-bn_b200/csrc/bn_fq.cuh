@@ -188,6 +188,51 @@ BN_HD void fq_sub(Fq& r, const Fq& a, const Fq& b) {  // src/arith.rs:290-296
     for (int i = 0; i < 8; i++) r.v[i] = t[i];
 #endif
 }
+// r = 9a + b  /  9a - b  mod q in one pass (the halves of a multiplication by xi = 9 + u, src/fields/fq2.rs:55-57):
+// t = 9a + b' < 10q over 9 limbs (b' = b or q - b), quotient estimate k from the top 16 bits with
+// k <= floor(t/q) <= k + 1, r = t - k q (< 2q, formed modulo 2^256), one conditional subtraction.
+// tools/gen_fq_ptx.py sweeps the estimate exhaustively over its 16-bit input.
+template <bool MINUS> BN_HD void fq_lin9(Fq& r, const Fq& a, const Fq& b) {
+#if defined(__CUDA_ARCH__)
+    uint32_t t[8];
+    if (MINUS) fq_9a_minus_b_ptx(t, a.v, b.v); else fq_9a_plus_b_ptx(t, a.v, b.v);
+#pragma unroll
+    for (int i = 0; i < 8; i++) r.v[i] = t[i];
+#else
+    uint32_t bp[8], t[9];
+    if (MINUS) {
+        int64_t br = 0;
+        for (int i = 0; i < 8; i++) {
+            int64_t d = (int64_t)fq_modulus_limb(i) - b.v[i] + br;
+            bp[i] = (uint32_t)d;
+            br = d >> 32;
+        }
+    } else {
+        for (int i = 0; i < 8; i++) bp[i] = b.v[i];
+    }
+    uint64_t c = 0;
+    for (int i = 0; i < 8; i++) {
+        uint64_t s = (uint64_t)a.v[i] * 9u + bp[i] + c;
+        t[i] = (uint32_t)s;
+        c = s >> 32;
+    }
+    t[8] = (uint32_t)c;
+    uint32_t th = (t[8] << 14) | (t[7] >> 18);
+    uint32_t k = (uint32_t)(((uint64_t)th * 1386367u) >> 32);     // floor(2^32 / 3098), 3097 = q >> 242
+    int64_t br = 0;
+    uint64_t mc = 0;
+    uint32_t o[8];
+    for (int i = 0; i < 8; i++) {
+        uint64_t m = (uint64_t)fq_modulus_limb(i) * k + mc;
+        mc = m >> 32;
+        int64_t d = (int64_t)t[i] - (int64_t)(uint32_t)m + br;
+        o[i] = (uint32_t)d;
+        br = d >> 32;
+    }
+    if (hostimpl::geq_q(o)) hostimpl::sub_q(o);
+    for (int i = 0; i < 8; i++) r.v[i] = o[i];
+#endif
+}
 BN_HD void fq_neg(Fq& r, const Fq& a) {  // src/arith.rs:309-316 (0 -> 0)
     Fq z;
     fq_set_zero(z);

@@ -123,11 +123,8 @@ BN_HD_NOINLINE void fq2_scale(Fq2& r, const Fq2& a, const Fq& k) {   // src/fiel
 // a * (9 + u) = (9 a0 - a1) + (9 a1 + a0) u; value of src/fields/fq2.rs:55-57
 BN_ADD_FN void fq2_mul_by_xi(Fq2& r, const Fq2& aa) {
     Fq2 a = fq2_ld(aa), n;
-    Fq t0, t1;
-    fq_dbl(t0, a.c0); fq_dbl(t0, t0); fq_dbl(t0, t0); fq_add(t0, t0, a.c0);   // 9 a0
-    fq_dbl(t1, a.c1); fq_dbl(t1, t1); fq_dbl(t1, t1); fq_add(t1, t1, a.c1);   // 9 a1
-    fq_sub(n.c0, t0, a.c1);
-    fq_add(n.c1, t1, a.c0);
+    fq_lin9<true>(n.c0, a.c0, a.c1);      // 9 a0 - a1
+    fq_lin9<false>(n.c1, a.c1, a.c0);     // 9 a1 + a0
     fq2_st(r, n);
 }
 BN_HD_NOINLINE bool fq2_inv(Fq2& r, const Fq2& a) {   // src/fields/fq2.rs:119-130

@@ -108,6 +108,9 @@ class Prog:
             if op == "and":
                 env[dst] = v[0] & v[1]
                 continue
+            if op == "shr":
+                env[dst] = v[0] >> v[1]
+                continue
             base, *mods = op.split(".")
             if base in ("mad", "madc"):
                 half = mods[0]
@@ -170,6 +173,8 @@ class Prog:
                 lines.append("%sselp.u32 %s, %s;" % (g, o(dst), ", ".join(o(s) for s in srcs)))
             elif op == "and":
                 lines.append("%sand.b32 %s, %s;" % (g, o(dst), ", ".join(o(s) for s in srcs)))
+            elif op == "shr":
+                lines.append("%sshr.u32 %s, %s;" % (g, o(dst), ", ".join(o(s) for s in srcs)))
             else:
                 lines.append("%s%s.u32 %s, %s;" % (g, op, o(dst), ", ".join(o(s) for s in srcs)))
         return lines
@@ -367,6 +372,65 @@ def gen_sub():
     return P
 
 
+NQL = [((1 << 256) - Q >> (32 * i)) & M32 for i in range(8)]     # 2^256 - q
+QH242 = Q >> 242                                                   # 3097
+KMUL = (1 << 32) // (QH242 + 1)                                    # floor(2^32 / 3098)
+
+
+def gen_lin9(minus):
+    """r = 9a + b (minus=False) or 9a - b (minus=True) mod q, fully reduced: the two halves of a multiplication
+    by xi = 9 + u in Fq2 (src/fields/fq2.rs:55-57), replacing four doublings/additions and a final add/sub, each
+    with its own conditional subtraction.
+
+    t = 9a + b' (b' = b or q - b) < 10q as 9 limbs: the products 9*a_j of the even limbs run as one carry chain on
+    top of b', those of the odd limbs are carry-free, one 8-limb addition joins them.  Quotient estimate from
+    the top 16 bits, k = ((t >> 242) * floor(2^32 / 3098)) >> 32, never above floor(t / q) and at most one below
+    (t / q - k < 1.01, argued in DESIGN.md F10 and swept by the simulator), so t - k*q < 2q fits 256 bits: it is
+    formed modulo 2^256 as t + k * (2^256 - q) with two more chains, then the usual conditional subtraction."""
+    P = Prog("fq_9a_minus_b_ptx" if minus else "fq_9a_plus_b_ptx")
+    a = ["a%d" % i for i in range(8)]
+    b = ["b%d" % i for i in range(8)]
+    r = ["r%d" % i for i in range(8)]
+    P.inputs = a + b
+    P.outputs = r
+    e = [P.tmp() for _ in range(9)]
+    if minus:                                  # e = q - b  (b < q: no borrow out)
+        for i in range(8):
+            P.emit("sub.cc" if i == 0 else ("subc.cc" if i < 7 else "subc"), e[i], QL[i], b[i])
+    # even chain: e += 9 * (a0 + a2 2^64 + a4 2^128 + a6 2^192)
+    for j in range(4):
+        src_lo = e[2 * j] if minus else b[2 * j]
+        src_hi = e[2 * j + 1] if minus else b[2 * j + 1]
+        P.emit("mad.lo.cc" if j == 0 else "madc.lo.cc", e[2 * j], a[2 * j], 9, src_lo)
+        P.emit("madc.hi.cc", e[2 * j + 1], a[2 * j], 9, src_hi)
+    P.emit("addc", e[8], 0, 0)
+    # odd products: limbs (1,2), (3,4), (5,6), (7,8), no carries between them
+    o = {}
+    for j in range(4):
+        lo, hi = P.tmp(), P.tmp()
+        P.emit("mul.lo", lo, a[2 * j + 1], 9)
+        P.emit("mul.hi", hi, a[2 * j + 1], 9)
+        o[2 * j + 1], o[2 * j + 2] = lo, hi
+    t = [e[0]] + [P.tmp() for _ in range(8)]
+    for p in range(1, 9):
+        P.emit("add.cc" if p == 1 else ("addc.cc" if p < 8 else "addc"), t[p], e[p], o[p])
+    # quotient estimate
+    x, th, k = P.tmp(), P.tmp(), P.tmp()
+    P.emit("shr", x, t[7], 18)
+    P.emit("mad.lo", th, t[8], 1 << 14, x)
+    P.emit("mul.hi", k, th, KMUL)
+    # r = t + k * (2^256 - q)  mod 2^256
+    for j in range(4):                         # even limbs of 2^256 - q
+        P.emit("mad.lo.cc" if j == 0 else "madc.lo.cc", r[2 * j], NQL[2 * j], k, t[2 * j])
+        P.emit("madc.hi.cc", r[2 * j + 1], NQL[2 * j], k, t[2 * j + 1])
+    for j in range(4):                         # odd limbs; the product at limb 7 keeps only its low half
+        P.emit("mad.lo.cc" if j == 0 else "madc.lo.cc", r[2 * j + 1], NQL[2 * j + 1], k, r[2 * j + 1])
+        if j < 3:
+            P.emit("madc.hi.cc", r[2 * j + 2], NQL[2 * j + 1], k, r[2 * j + 2])
+    cond_sub_q(P, r)
+    return P
+
+
 def gen_wide_add():
     P = Prog("wide_add_ptx")
     a = ["a%d" % i for i in range(16)]
@@ -447,8 +511,47 @@ def check():
         assert got == (t - u if t >= u else t - u + Q * R), "wide_sub"
         if t + u < (1 << 512):
             assert unl(pwa.run(env), pwa.outputs) == t + u, "wide_add"
-    print("simulated OK: %d mul/mulwide/add/sub pairs, 2000 redc/wide cases" % n)
-    for p in (pm, pw, pr, pa, ps):
+    pp, pn = gen_lin9(False), gen_lin9(True)
+    nl = 0
+    # sweep the quotient estimate: 9a + b (and 9a + q - b) just below / at / above every multiple of q, plus random pairs
+    targets = []
+    for kq in range(0, 11):
+        for d in (-2, -1, 0, 1, 2, (1 << 224) - 1, -(1 << 224), 1 << 242, -(1 << 242)):
+            targets.append(kq * Q + d)
+    for tgt in targets:
+        for _ in range(6):
+            # 9a + b = tgt with 0 <= a, b < q
+            a_hi = min(Q - 1, tgt // 9) if tgt >= 0 else -1
+            a_lo = max(0, -(-(tgt - (Q - 1)) // 9))
+            if a_hi < a_lo:
+                continue
+            a9 = rng.randrange(a_lo, a_hi + 1)
+            bb = tgt - 9 * a9
+            if not 0 <= bb < Q:
+                continue
+            env = {("a%d" % i): v for i, v in enumerate(limbs(a9, 8))}
+            env.update({("b%d" % i): v for i, v in enumerate(limbs(bb, 8))})
+            assert unl(pp.run(env), pp.outputs) == (9 * a9 + bb) % Q, ("9a+b", hex(a9), hex(bb))
+            nb = (Q - bb) % Q if bb else 0          # 9a - nb = 9a + bb - q  (same t when bb != 0)
+            env.update({("b%d" % i): v for i, v in enumerate(limbs(nb, 8))})
+            assert unl(pn.run(env), pn.outputs) == (9 * a9 - nb) % Q, ("9a-b", hex(a9), hex(nb))
+            nl += 2
+    for a9 in vals:
+        for bb in (vals if a9 in edge else rng.sample(vals, 12)):
+            env = {("a%d" % i): v for i, v in enumerate(limbs(a9, 8))}
+            env.update({("b%d" % i): v for i, v in enumerate(limbs(bb, 8))})
+            assert unl(pp.run(env), pp.outputs) == (9 * a9 + bb) % Q, ("9a+b", hex(a9), hex(bb))
+            assert unl(pn.run(env), pn.outputs) == (9 * a9 - bb) % Q, ("9a-b", hex(a9), hex(bb))
+            nl += 2
+    # the estimate itself, exhaustively over the 16-bit top word: k <= floor(t/q) <= k + 1 for every t with that top
+    for th in range(0, (10 * Q >> 242) + 2):
+        k = (th * KMUL) >> 32
+        lo_t, hi_t = th << 242, min(((th + 1) << 242) - 1, 10 * Q - 1)
+        if lo_t > hi_t:
+            continue
+        assert k <= lo_t // Q and hi_t // Q <= k + 1 and hi_t - k * Q < 2 * Q, th
+    print("simulated OK: %d mul/mulwide/add/sub pairs, 2000 redc/wide cases, %d 9a+-b cases" % (n, nl))
+    for p in (pm, pw, pr, pa, ps, pp, pn):
         ops = [op.split(".")[0] for op, _, _, _ in p.ins]
         print("  %-16s %3d PTX instrs (%d mad/mul)" % (p.name, len(p.ins), sum(o in ("mad", "madc", "mul") for o in ops)))
 
@@ -486,7 +589,7 @@ def main():
                 "// generation time.  8x32-bit-limb BN254 Fq arithmetic as single inline-PTX carry-chain blocks.\n"
                 "// Outputs are early-clobber ('=&r'): they never alias an input register.\n"
                 "#pragma once\n#include <stdint.h>\n\n")
-        for P, io in ((gen_mul(), False), (gen_mulwide(), False), (gen_redc(), False), (gen_add(), False), (gen_sub(), False),
+        for P, io in ((gen_mul(), False), (gen_mulwide(), False), (gen_redc(), False), (gen_add(), False), (gen_sub(), False), (gen_lin9(False), False), (gen_lin9(True), False),
                       (gen_wide_add(), True), (gen_wide_sub(), True)):
             f.write(emit_function(P, io))
             f.write("\n")
