@@ -18,8 +18,17 @@ G2PRECOMP = 128 + 87 * 192
 
 
 def build(force=False):
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(os.path.join(_HERE, "bn254_oracle.c")):
-        subprocess.check_call(["make", "-s", "-C", _HERE] + (["-B"] if force else []))
+    """Compile the oracle if missing or stale.  Serialised with a lock file and installed by an atomic rename, so
+    concurrent processes (the two ranks of the gloo test on a fresh checkout) never load a half-written library."""
+    import fcntl
+    src = os.path.join(_HERE, "bn254_oracle.c")
+    os.makedirs(os.path.dirname(_SO), exist_ok=True)
+    with open(os.path.join(os.path.dirname(_SO), ".lock"), "w") as lk:
+        fcntl.flock(lk, fcntl.LOCK_EX)
+        if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+            tmp = "%s.tmp.%d" % (_SO, os.getpid())
+            subprocess.check_call(["make", "-s", "-C", _HERE, "OUT=" + tmp] + (["-B"] if force else []))
+            os.replace(tmp, _SO)
     return _SO
 
 

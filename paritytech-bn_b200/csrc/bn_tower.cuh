@@ -383,10 +383,43 @@ BN_HD_NOINLINE void fq12_cyclotomic_sqr_na(Fq12& r, const Fq12& a) {
     fq2_sub(r.c0.c1, t2, a.c0.c1); fq2_dbl(r.c0.c1, r.c0.c1); fq2_add(r.c0.c1, r.c0.c1, t2);   // z4' = 3 t2 - 2 z4
     fq2_add(r.c1.c2, t3, a.c1.c2); fq2_dbl(r.c1.c2, r.c1.c2); fq2_add(r.c1.c2, r.c1.c2, t3);   // z5' = 3 t3 + 2 z5
 }
+// Width-4 recoding of the same u: digits in {0, +-1, +-3, +-5, +-7}, 14 non-zero (13 multiplications + 3 for
+// a^3, a^5, a^7).  Bits W4_I0/W4_I1 of position i give (|d_i| - 1) / 2.  The default; -DBN_U_WINDOW=3 selects the width-3 digits.
+#define BN_U_WNAF4_NZ 0x4108844442110211ull
+#define BN_U_WNAF4_NEG 0x0008004400010010ull
+#define BN_U_WNAF4_I0 0x0008800400110000ull
+#define BN_U_WNAF4_I1 0x0100044002110200ull
+#ifndef BN_U_WINDOW
+#define BN_U_WINDOW 4
+#endif
 BN_HD_NOINLINE void fq12_exp_by_neg_z(Fq12& r, const Fq12& a) {
     // Two accumulators used alternately (every step reads one and writes the other).  The buffers are named
     // statically in both branches -- a pointer table here makes nvcc lose the local address space of EVERY
     // Fq2-level body (generic LD/ST instead of LDL/STL: -5 % on all kernels, measured).
+#if BN_U_WINDOW == 4
+    Fq12 a3, a5, a7, buf0, buf1;
+    fq12_cyclotomic_sqr_na(buf0, a);               // a^2
+    fq12_mul_na(a3, buf0, a, false);
+    fq12_mul_na(a5, buf0, a3, false);
+    fq12_mul_na(a7, buf0, a5, false);
+    bool in0 = true;                               // top digit (bit 62) is +1; buf0 already holds a^2 (step i = 61)
+    for (int i = 61; i >= 0; i--) {
+        if (i != 61) {
+            if (in0) fq12_cyclotomic_sqr_na(buf1, buf0); else fq12_cyclotomic_sqr_na(buf0, buf1);
+            in0 = !in0;
+        }
+        if ((BN_U_WNAF4_NZ >> i) & 1) {
+            bool neg = ((BN_U_WNAF4_NEG >> i) & 1) != 0;
+            int idx = (int)((BN_U_WNAF4_I0 >> i) & 1) | ((int)((BN_U_WNAF4_I1 >> i) & 1) << 1);
+            if (idx == 0) { if (in0) fq12_mul_na(buf1, buf0, a, neg); else fq12_mul_na(buf0, buf1, a, neg); }
+            else if (idx == 1) { if (in0) fq12_mul_na(buf1, buf0, a3, neg); else fq12_mul_na(buf0, buf1, a3, neg); }
+            else if (idx == 2) { if (in0) fq12_mul_na(buf1, buf0, a5, neg); else fq12_mul_na(buf0, buf1, a5, neg); }
+            else { if (in0) fq12_mul_na(buf1, buf0, a7, neg); else fq12_mul_na(buf0, buf1, a7, neg); }
+            in0 = !in0;
+        }
+    }
+    if (in0) fq12_conj(r, buf0); else fq12_conj(r, buf1);
+#else
     Fq12 a3, buf0, buf1;
     fq12_cyclotomic_sqr_na(buf0, a);
     fq12_mul_na(a3, buf0, a, false);
@@ -408,6 +441,7 @@ BN_HD_NOINLINE void fq12_exp_by_neg_z(Fq12& r, const Fq12& a) {
         }
     }
     if (in0) fq12_conj(r, buf0); else fq12_conj(r, buf1);
+#endif
 }
 // easy part f^((q^6-1)(q^2+1)); false iff f == 0.  src/fields/fq12.rs:62-73
 BN_HD_NOINLINE bool fq12_final_exp_first_chunk(Fq12& r, const Fq12& f) {

@@ -153,6 +153,24 @@ def test_wnaf3_recoding_of_u_in_device_header():
     assert m["NEG"] & ~m["NZ"] == 0 and m["M3"] & ~m["NZ"] == 0 and (m["NZ"] >> 62) == 1 and not (m["NEG"] >> 62) & 1
 
 
+def test_wnaf4_recoding_of_u_in_device_header():
+    """The width-4 digits (default window of fq12_exp_by_neg_z): magnitude 2 * (I1 I0) + 1, 14 non-zero digits."""
+    import os
+    import re
+    src = open(os.path.join(os.path.dirname(__file__), "..", "paritytech-bn_b200", "csrc", "bn_tower.cuh")).read()
+    m = {k: int(re.search(r"#define BN_U_WNAF4_%s (0x[0-9a-f]+)ull" % k, src).group(1), 16) for k in ("NZ", "NEG", "I0", "I1")}
+    v, nz = 0, 0
+    for i in range(64):
+        if (m["NZ"] >> i) & 1:
+            d = 2 * (((m["I0"] >> i) & 1) | (((m["I1"] >> i) & 1) << 1)) + 1
+            v += (-d if (m["NEG"] >> i) & 1 else d) << i
+            nz += 1
+    assert v == 4965661367192848881 and nz == 14          # src/fields/fq12.rs:122
+    assert (m["NEG"] | m["I0"] | m["I1"]) & ~m["NZ"] == 0
+    assert (m["NZ"] >> 62) == 1 and not ((m["NEG"] | m["I0"] | m["I1"]) >> 62) & 1   # top digit is +1
+    assert re.search(r"#define BN_U_WINDOW 4", src)
+
+
 def test_doubling_mask_matches_naf():
     """BN_DBL_MASK_* in bn_curve.cuh marks exactly the doubling-step coefficients of precompute()'s 87 triples."""
     import os
