@@ -128,3 +128,14 @@ def test_psi_subgroup_test_matches_reference_ladder(eng):
     assert fast.tobytes() == slow.tobytes() == c.g2_affine_check(a2).tobytes()
     assert set(fast[-240:]) == {2} and int((fast == 0).sum()) > 400
     assert s1.tobytes() == s2.tobytes() and o1.tobytes() == o2.tobytes()
+
+
+def test_every_entry_point_at_a_ragged_size():
+    """scripts/all_entry_points.py: each host-buffer entry point at n = 70 (block size 64) against the oracle."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    p = subprocess.run([sys.executable, os.path.join(root, "scripts", "all_entry_points.py"), "70"], capture_output=True, text=True,
+                       timeout=900, cwd=root)
+    assert p.returncode == 0 and "every entry point ran" in p.stdout, p.stdout[-1000:] + p.stderr[-3000:]
