@@ -38,6 +38,7 @@ struct bn254_ctx {
     size_t ws_bytes;
     int split_miller;  // 1: three-kernel Miller path (default), 0: fused single kernel (BN254_FUSED_MILLER=1)
     int split_fexp;    // 1: easy + hard final-exponentiation kernels (BN254_SPLIT_FEXP=1), 0: one kernel
+    bool zerocopy_out; // pinned output buffers are written by the last kernel directly (BN254_ZEROCOPY_OUT=0 disables)
     bool subgroup_ref; // true: G2 order check with the reference's [r-1]P + P ladder (BN254_SUBGROUP_REF=1); false: psi test
 };
 struct bn254_g2precomp {
@@ -76,6 +77,12 @@ static int use(bn254_ctx* ctx) {
     CU(cudaSetDevice(ctx->device));
     return 0;
 }
+// device-side alias of a pinned, mapped host buffer (cudaHostAlloc / cudaHostRegister under UVA); nullptr for pageable memory
+static void* mapped_device_ptr(const void* host) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, host) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+    return (a.type == cudaMemoryTypeHost) ? a.devicePointer : nullptr;
+}
 static int h2d(bn254_ctx* ctx, void* d, const void* h, size_t bytes) {
     if (bytes) CU(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, ctx->stream));
     return 0;
@@ -112,6 +119,7 @@ int bn254_ctx_create(int device, bn254_ctx** out) {
     { const char* e = getenv("BN254_FUSED_MILLER"); c->split_miller = (e && e[0] == '1') ? 0 : 1; }
     { const char* e = getenv("BN254_SPLIT_FEXP"); c->split_fexp = (e && e[0] == '1') ? 1 : 0; }
     { const char* e = getenv("BN254_SUBGROUP_REF"); c->subgroup_ref = (e && e[0] == '1'); }
+    { const char* e = getenv("BN254_ZEROCOPY_OUT"); c->zerocopy_out = !(e && e[0] == '0'); }
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { delete c; return fail(BN254_ERR_CUDA, "cudaStreamCreate", e); }
     // deep call chains (Fq12 -> Fq6 -> Fq2 noinline bodies) need more than the default stack
@@ -278,8 +286,16 @@ int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_
     TRY(ctx_io(ctx, sz, 3, d));
     TRY(h2d(ctx, d[0], g1, sz[0]));
     TRY(h2d(ctx, d[1], g2, sz[1]));
-    TRY(bn254_pairing_many_dev(ctx, d[0], d[1], d[2], n));
-    TRY(d2h(ctx, gt_out, d[2], sz[2]));
+    // Pinned (mapped) output buffer: the final-exponentiation kernel stores its 384-byte results straight into host
+    // memory, so the device-to-host transfer rides under the 12 ms kernel instead of following it.
+    void* mapped = ctx->zerocopy_out ? mapped_device_ptr(gt_out) : nullptr;
+    if (mapped) {
+        TRY(miller_many_dev(ctx, (const G2*)d[1], (const G1*)d[0], (Fq12*)d[2], (uint8_t*)nullptr, n));
+        TRY(final_exp_dev(ctx, (const Fq12*)d[2], (Fq12*)mapped, (uint8_t*)nullptr, (uint8_t*)nullptr, n));
+    } else {
+        TRY(bn254_pairing_many_dev(ctx, d[0], d[1], d[2], n));
+        TRY(d2h(ctx, gt_out, d[2], sz[2]));
+    }
     CU(cudaStreamSynchronize(ctx->stream));
     return 0;
 }
