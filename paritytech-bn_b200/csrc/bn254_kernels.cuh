@@ -40,7 +40,7 @@ __device__ __noinline__ bool pair_to_affine(AffG1& pa, AffG2& qa, const G1& p, c
     fq_mul(t, q.z.c1, q.z.c1);
     fq_add(n, n, t);                 // norm(q.z) != 0
     fq_mul_ni(t, p.z, n);
-    fq_inv(ti, t);
+    fq_inv_w4(ti, t);
     fq_mul_ni(pzi, ti, n);           // 1/p.z
     fq_mul_ni(ni, ti, p.z);          // 1/norm
     fq_mul_ni(z2, pzi, pzi);

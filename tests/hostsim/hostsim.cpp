@@ -32,6 +32,9 @@ UN(g1_normalize, G1, jac_normalize) UN(g2_normalize, G2, jac_normalize)
 extern "C" void hs_fq_inv(const void* a, void* o, unsigned char* some, size_t n) {
     for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r; some[i] = fq_inv(r, x); st(o, i, r); }
 }
+extern "C" void hs_fq_inv_w4(const void* a, void* o, unsigned char* some, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r; some[i] = fq_inv_w4(r, x); st(o, i, r); }
+}
 extern "C" void hs_fq12_inv(const void* a, void* o, unsigned char* some, size_t n) {
     for (size_t i = 0; i < n; i++) { Fq12 x = ld<Fq12>(a, i), r; some[i] = fq12_inv(r, x); st(o, i, r); }
 }
