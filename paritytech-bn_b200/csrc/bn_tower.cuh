@@ -389,18 +389,20 @@ BN_HD_NOINLINE void fq12_mul_na(Fq12& r, const Fq12& a, const Fq12& b, bool conj
     else { fq6_sub(r.c1, r.c1, bb); fq6_add(r.c0, r.c0, aa); }
 }
 BN_HD_NOINLINE void fq12_cyclotomic_sqr_na(Fq12& r, const Fq12& a) {
-    // reference labels (fq12.rs:199-204): z0 = c0.c0, z4 = c0.c1, z3 = c0.c2, z2 = c1.c0, z1 = c1.c1, z5 = c1.c2
-    Fq2 t0, t1, t2, t3, t4, t5;
+    // reference labels (fq12.rs:199-204): z0 = c0.c0, z4 = c0.c1, z3 = c0.c2, z2 = c1.c0, z1 = c1.c1, z5 = c1.c2.
+    // One coefficient pair at a time, its two results written before the next pair starts: two live temporaries
+    // instead of six, and each input coefficient is re-read while it is still in L1.
+    Fq2 t0, t1;
     fq4_sqr(t0, t1, a.c0.c0, a.c1.c1);
-    fq4_sqr(t2, t3, a.c1.c0, a.c0.c2);
-    fq4_sqr(t4, t5, a.c0.c1, a.c1.c2);
     fq2_sub(r.c0.c0, t0, a.c0.c0); fq2_dbl(r.c0.c0, r.c0.c0); fq2_add(r.c0.c0, r.c0.c0, t0);   // z0' = 3 t0 - 2 z0
     fq2_add(r.c1.c1, t1, a.c1.c1); fq2_dbl(r.c1.c1, r.c1.c1); fq2_add(r.c1.c1, r.c1.c1, t1);   // z1' = 3 t1 + 2 z1
-    fq2_mul_by_xi(t5, t5);
-    fq2_add(r.c1.c0, t5, a.c1.c0); fq2_dbl(r.c1.c0, r.c1.c0); fq2_add(r.c1.c0, r.c1.c0, t5);   // z2' = 3 xi t5 + 2 z2
-    fq2_sub(r.c0.c2, t4, a.c0.c2); fq2_dbl(r.c0.c2, r.c0.c2); fq2_add(r.c0.c2, r.c0.c2, t4);   // z3' = 3 t4 - 2 z3
-    fq2_sub(r.c0.c1, t2, a.c0.c1); fq2_dbl(r.c0.c1, r.c0.c1); fq2_add(r.c0.c1, r.c0.c1, t2);   // z4' = 3 t2 - 2 z4
-    fq2_add(r.c1.c2, t3, a.c1.c2); fq2_dbl(r.c1.c2, r.c1.c2); fq2_add(r.c1.c2, r.c1.c2, t3);   // z5' = 3 t3 + 2 z5
+    fq4_sqr(t0, t1, a.c1.c0, a.c0.c2);                                                         // (t2, t3)
+    fq2_sub(r.c0.c1, t0, a.c0.c1); fq2_dbl(r.c0.c1, r.c0.c1); fq2_add(r.c0.c1, r.c0.c1, t0);   // z4' = 3 t2 - 2 z4
+    fq2_add(r.c1.c2, t1, a.c1.c2); fq2_dbl(r.c1.c2, r.c1.c2); fq2_add(r.c1.c2, r.c1.c2, t1);   // z5' = 3 t3 + 2 z5
+    fq4_sqr(t0, t1, a.c0.c1, a.c1.c2);                                                         // (t4, t5)
+    fq2_sub(r.c0.c2, t0, a.c0.c2); fq2_dbl(r.c0.c2, r.c0.c2); fq2_add(r.c0.c2, r.c0.c2, t0);   // z3' = 3 t4 - 2 z3
+    fq2_mul_by_xi(t1, t1);
+    fq2_add(r.c1.c0, t1, a.c1.c0); fq2_dbl(r.c1.c0, r.c1.c0); fq2_add(r.c1.c0, r.c1.c0, t1);   // z2' = 3 xi t5 + 2 z2
 }
 // Width-4 recoding of the same u: digits in {0, +-1, +-3, +-5, +-7}, 14 non-zero (13 multiplications + 3 for
 // a^3, a^5, a^7).  Bits W4_I0/W4_I1 of position i give (|d_i| - 1) / 2.  The default; -DBN_U_WINDOW=3 selects the width-3 digits.
