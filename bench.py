@@ -305,6 +305,10 @@ def main():
                                      "algorithmic bytes per launch = %d (Gt in + Gt out)" % (2 * GT * n),
                      "peak_source": "measured in this run (register-only mad.lo chains, 64 IMAD/clk/SM); an IMAD.WIDE counts 2 IMAD-eq (measured 4.1 clk/warp-inst "
                                     "vs 2.0 for IMAD, profiles/r01_pipe_microbench2.txt); MEASURED_PEAKS.json has no integer peak",
+                     "hbm": ({"achieved": traffic * n / (dom_ms * 1e-3) / 1e9, "peak": HBM_PEAK_GBS, "unit": "GB/s",
+                              "frac": traffic * n / (dom_ms * 1e-3) / 1e9 / HBM_PEAK_GBS,
+                              "note": "local-memory (Fq12 working set) spill traffic of that kernel, not algorithmic I/O: HBM is not the bound"}
+                             if traffic else None),
                      "peak_theoretical": sms * 64 * sm_mhz * 1e6 / 1e12 if sm_mhz else None,
                      "algorithmic_imad_eq_per_pairing": FQMUL_PAIRING * FQMUL_IMAD_EQ,
                      "whole_step_frac": FQMUL_PAIRING * FQMUL_IMAD_EQ * n * world * args.steps / (total_ms * 1e-3) / (peak_measured * world),
