@@ -127,6 +127,9 @@ int bn254_g2_normalize_many(bn254_ctx* ctx, const void* g2, void* g2_out, size_t
 #define BN254_AFFINE_NOT_IN_SUBGROUP 2
 int bn254_g1_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n);
 int bn254_g2_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n);
+/* device-pointer twins (asynchronous on the context's stream): validate points that are already in HBM */
+int bn254_g1_affine_check_many_dev(bn254_ctx* ctx, const void* d_xy, uint8_t* d_status, size_t n);
+int bn254_g2_affine_check_many_dev(bn254_ctx* ctx, const void* d_xy, uint8_t* d_status, size_t n);
 
 /* ---- G1::from_compressed src/lib.rs:359-375, G2::from_compressed :506-526 ---- */
 /* enc: n records of 33 bytes (G1: tag 2/3, x big-endian) or 65 bytes (G2: tag 10/11, x = c1*q + c0 as a
@@ -141,6 +144,10 @@ int bn254_g2_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, 
 #define BN254_DECODE_FIELD_NOT_MEMBER 3
 int bn254_g1_from_compressed_many(bn254_ctx* ctx, const uint8_t* enc, void* g1_out, uint8_t* status, size_t n);
 int bn254_g2_from_compressed_many(bn254_ctx* ctx, const uint8_t* enc, void* g2_out, uint8_t* status, size_t n);
+/* device-pointer twins: the decoded images stay in HBM and can be handed to bn254_pairing_many_dev and friends
+ * (a failed record is all-zero, i.e. z = 0: the pairing entry points treat it as the point at infinity) */
+int bn254_g1_from_compressed_many_dev(bn254_ctx* ctx, const uint8_t* d_enc, void* d_g1_out, uint8_t* d_status, size_t n);
+int bn254_g2_from_compressed_many_dev(bn254_ctx* ctx, const uint8_t* d_enc, void* d_g2_out, uint8_t* d_status, size_t n);
 
 /* ---- shared G2Precomp: src/groups/mod.rs:573-577, :701-728 ------------------------------------- */
 /* Precompute the 87 line-coefficient triples of n G2 points once; the tables stay on the device.

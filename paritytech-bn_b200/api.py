@@ -347,6 +347,20 @@ class Engine:
         self._check(self.lib.bn254_g2_mul_many_dev(self.ctx, ctypes.c_void_p(d_g2), ctypes.c_void_p(d_fr),
                                                    ctypes.c_void_p(d_out), ctypes.c_size_t(n)))
 
+    def g1_from_compressed_dev(self, d_enc, d_out, d_status, n):
+        self._check(self.lib.bn254_g1_from_compressed_many_dev(self.ctx, ctypes.c_void_p(d_enc), ctypes.c_void_p(d_out),
+                                                               ctypes.c_void_p(d_status), ctypes.c_size_t(n)))
+
+    def g2_from_compressed_dev(self, d_enc, d_out, d_status, n):
+        self._check(self.lib.bn254_g2_from_compressed_many_dev(self.ctx, ctypes.c_void_p(d_enc), ctypes.c_void_p(d_out),
+                                                               ctypes.c_void_p(d_status), ctypes.c_size_t(n)))
+
+    def g1_affine_check_dev(self, d_xy, d_status, n):
+        self._check(self.lib.bn254_g1_affine_check_many_dev(self.ctx, ctypes.c_void_p(d_xy), ctypes.c_void_p(d_status), ctypes.c_size_t(n)))
+
+    def g2_affine_check_dev(self, d_xy, d_status, n):
+        self._check(self.lib.bn254_g2_affine_check_many_dev(self.ctx, ctypes.c_void_p(d_xy), ctypes.c_void_p(d_status), ctypes.c_size_t(n)))
+
     # ---- test hooks / microbenchmarks ------------------------------------------------------------------
     def field_op(self, name, a, b=None):
         op, unit = FIELD_OPS[name]

@@ -617,6 +617,17 @@ int bn254_g2_normalize_many(bn254_ctx* ctx, const void* g2, void* out, size_t n)
     return 0;
 }
 
+static int affine_check_dev(bn254_ctx* ctx, const void* d_xy, uint8_t* d_status, size_t n, bool g2) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!d_xy || !d_status) return fail(BN254_ERR_ARG, "null pointer");
+    if (g2) {
+        LAUNCH(ctx, k_g2_affine_check, n, (const AffG2*)d_xy, d_status, n, ctx->subgroup_ref);
+    } else {
+        LAUNCH(ctx, k_g1_affine_check, n, (const AffG1*)d_xy, d_status, n);
+    }
+    return 0;
+}
 static int affine_check_host(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n, bool g2) {
     TRY(use(ctx));
     if (n == 0) return 0;
@@ -625,11 +636,7 @@ static int affine_check_host(bn254_ctx* ctx, const void* xy, uint8_t* status, si
     void* d[2];
     TRY(ctx_io(ctx, sz, 2, d));
     TRY(h2d(ctx, d[0], xy, sz[0]));
-    if (g2) {
-        LAUNCH(ctx, k_g2_affine_check, n, (const AffG2*)d[0], (uint8_t*)d[1], n, ctx->subgroup_ref);
-    } else {
-        LAUNCH(ctx, k_g1_affine_check, n, (const AffG1*)d[0], (uint8_t*)d[1], n);
-    }
+    TRY(affine_check_dev(ctx, d[0], (uint8_t*)d[1], n, g2));
     TRY(d2h(ctx, status, d[1], n));
     CU(cudaStreamSynchronize(ctx->stream));
     return 0;
@@ -640,7 +647,24 @@ int bn254_g1_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, 
 int bn254_g2_affine_check_many(bn254_ctx* ctx, const void* xy, uint8_t* status, size_t n) {
     return affine_check_host(ctx, xy, status, n, true);
 }
+int bn254_g1_affine_check_many_dev(bn254_ctx* ctx, const void* d_xy, uint8_t* d_status, size_t n) {
+    return affine_check_dev(ctx, d_xy, d_status, n, false);
+}
+int bn254_g2_affine_check_many_dev(bn254_ctx* ctx, const void* d_xy, uint8_t* d_status, size_t n) {
+    return affine_check_dev(ctx, d_xy, d_status, n, true);
+}
 
+static int from_compressed_dev(bn254_ctx* ctx, const uint8_t* d_enc, void* d_out, uint8_t* d_status, size_t n, bool g2) {
+    TRY(use(ctx));
+    if (n == 0) return 0;
+    if (!d_enc || !d_out || !d_status) return fail(BN254_ERR_ARG, "null pointer");
+    if (g2) {
+        LAUNCH(ctx, k_g2_from_compressed, n, d_enc, (G2*)d_out, d_status, n, ctx->subgroup_ref);
+    } else {
+        LAUNCH(ctx, k_g1_from_compressed, n, d_enc, (G1*)d_out, d_status, n);
+    }
+    return 0;
+}
 static int from_compressed_host(bn254_ctx* ctx, const uint8_t* enc, void* out, uint8_t* status, size_t n, bool g2) {
     TRY(use(ctx));
     if (n == 0) return 0;
@@ -649,11 +673,7 @@ static int from_compressed_host(bn254_ctx* ctx, const uint8_t* enc, void* out, u
     void* d[3];
     TRY(ctx_io(ctx, sz, 3, d));
     TRY(h2d(ctx, d[0], enc, sz[0]));
-    if (g2) {
-        LAUNCH(ctx, k_g2_from_compressed, n, (const uint8_t*)d[0], (G2*)d[1], (uint8_t*)d[2], n, ctx->subgroup_ref);
-    } else {
-        LAUNCH(ctx, k_g1_from_compressed, n, (const uint8_t*)d[0], (G1*)d[1], (uint8_t*)d[2], n);
-    }
+    TRY(from_compressed_dev(ctx, (const uint8_t*)d[0], d[1], (uint8_t*)d[2], n, g2));
     TRY(d2h(ctx, out, d[1], sz[1]));
     TRY(d2h(ctx, status, d[2], n));
     CU(cudaStreamSynchronize(ctx->stream));
@@ -664,6 +684,12 @@ int bn254_g1_from_compressed_many(bn254_ctx* ctx, const uint8_t* enc, void* g1_o
 }
 int bn254_g2_from_compressed_many(bn254_ctx* ctx, const uint8_t* enc, void* g2_out, uint8_t* status, size_t n) {
     return from_compressed_host(ctx, enc, g2_out, status, n, true);
+}
+int bn254_g1_from_compressed_many_dev(bn254_ctx* ctx, const uint8_t* d_enc, void* d_g1_out, uint8_t* d_status, size_t n) {
+    return from_compressed_dev(ctx, d_enc, d_g1_out, d_status, n, false);
+}
+int bn254_g2_from_compressed_many_dev(bn254_ctx* ctx, const uint8_t* d_enc, void* d_g2_out, uint8_t* d_status, size_t n) {
+    return from_compressed_dev(ctx, d_enc, d_g2_out, d_status, n, true);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -139,3 +139,46 @@ def test_every_entry_point_at_a_ragged_size():
     p = subprocess.run([sys.executable, os.path.join(root, "scripts", "all_entry_points.py"), "70"], capture_output=True, text=True,
                        timeout=900, cwd=root)
     assert p.returncode == 0 and "every entry point ran" in p.stdout, p.stdout[-1000:] + p.stderr[-3000:]
+
+
+def test_decode_validate_pair_chain_stays_on_device(eng):
+    """Compressed records -> from_compressed_dev -> affine_check_dev -> pairing_many_dev without leaving HBM; the Gt
+    results equal the oracle's pairings of the original points, a corrupted record decodes to the all-zero image
+    (z = 0), which the pairing treats as the point at infinity (Gt::one), exactly like pairing(G1::zero(), q)."""
+    import torch
+    n = 200
+    g1, g2, e1, e2 = _compress_many(eng, n, 91)
+    e2 = bytearray(e2)
+    e2[65 * 7] = 0x0c                                           # invalid tag on record 7
+    dev = torch.device("cuda", 0)
+    stream = torch.cuda.ExternalStream(eng.stream, device=dev)
+    d_e1 = torch.frombuffer(bytearray(e1), dtype=torch.uint8).to(dev)
+    d_e2 = torch.frombuffer(e2, dtype=torch.uint8).to(dev)
+    d_g1 = torch.empty(n * 96, dtype=torch.uint8, device=dev)
+    d_g2 = torch.empty(n * 192, dtype=torch.uint8, device=dev)
+    d_s1 = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_s2 = torch.empty(n, dtype=torch.uint8, device=dev)
+    d_gt = torch.empty(n * 384, dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+    eng.g1_from_compressed_dev(d_e1.data_ptr(), d_g1.data_ptr(), d_s1.data_ptr(), n)
+    eng.g2_from_compressed_dev(d_e2.data_ptr(), d_g2.data_ptr(), d_s2.data_ptr(), n)
+    eng.pairing_dev(d_g1.data_ptr(), d_g2.data_ptr(), d_gt.data_ptr(), n)
+    eng.synchronize()
+    s1, s2 = d_s1.cpu().numpy(), d_s2.cpu().numpy()
+    assert not s1.any() and s2[7] == 1 and not np.delete(s2, 7).any()
+    g2x = g2.copy()
+    g2x[192 * 7:192 * 8] = 0
+    assert d_g2.cpu().numpy().tobytes() == g2x.tobytes() and d_g1.cpu().numpy().tobytes() == g1.tobytes()
+    got = d_gt.cpu().numpy()
+    g2inf = g2.copy()
+    g2inf[192 * 7:192 * 8] = util.G2_INF
+    assert got.tobytes() == c.pairing_many(g1, g2inf).tobytes()
+    assert got[384 * 7:384 * 8].tobytes() == util.GT_ONE.tobytes()
+    # validation twin on the decoded affine coordinates
+    xy = d_g2.view(n, 192)[:, :128].contiguous()
+    d_st = torch.empty(n, dtype=torch.uint8, device=dev)
+    torch.cuda.synchronize()
+    eng.g2_affine_check_dev(xy.data_ptr(), d_st.data_ptr(), n)
+    eng.synchronize()
+    st = d_st.cpu().numpy()
+    assert st[7] == 1 and not np.delete(st, 7).any()         # (0, 0) is not on the curve
