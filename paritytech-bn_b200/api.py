@@ -22,7 +22,7 @@ ERR_TO_AFFINE = 1
 
 FIELD_OPS = {"fq_mul": (0, 32), "fq_add": (1, 32), "fq_sub": (2, 32), "fq2_mul": (3, 64), "fq2_sqr": (4, 64),
              "fq6_mul": (5, 192), "fq12_mul": (6, 384), "fq12_sqr": (7, 384), "fq12_cyclotomic_sqr": (8, 384),
-             "fq_inv": (9, 32)}
+             "fq_inv": (9, 32), "fq2_mul_by_xi": (10, 64)}
 
 
 class BnError(RuntimeError):

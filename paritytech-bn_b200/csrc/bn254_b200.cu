@@ -834,8 +834,8 @@ int bn254_pairing_product_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1
 int bn254_field_op_many(bn254_ctx* ctx, int op, const void* a, const void* b, void* out, size_t n) {
     TRY(use(ctx));
     if (n == 0) return 0;
-    static const size_t unit_of[10] = {32, 32, 32, 64, 64, 192, 384, 384, 384, 32};
-    if (op < 0 || op > 9 || !a || !out) return fail(BN254_ERR_ARG, "bad argument");
+    static const size_t unit_of[11] = {32, 32, 32, 64, 64, 192, 384, 384, 384, 32, 64};
+    if (op < 0 || op > 10 || !a || !out) return fail(BN254_ERR_ARG, "bad argument");
     bool binary = (op == 0 || op == 1 || op == 2 || op == 3 || op == 5 || op == 6);
     if (binary && !b) return fail(BN254_ERR_ARG, "null pointer");
     size_t bytes = unit_of[op] * n;

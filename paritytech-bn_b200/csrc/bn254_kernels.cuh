@@ -456,9 +456,9 @@ BN_KERNEL k_field_op(int op, const uint4* __restrict__ a, const uint4* __restric
             }
             reinterpret_cast<Fq*>(out)[i] = r;
         } break;
-        case 3: case 4: {
+        case 3: case 4: case 10: {
             Fq2 x = reinterpret_cast<const Fq2*>(a)[i], r;
-            if (op == 3) { Fq2 y = reinterpret_cast<const Fq2*>(b)[i]; fq2_mul(r, x, y); } else fq2_sqr(r, x);
+            if (op == 3) { Fq2 y = reinterpret_cast<const Fq2*>(b)[i]; fq2_mul(r, x, y); } else if (op == 4) fq2_sqr(r, x); else fq2_mul_by_xi(r, x);
             reinterpret_cast<Fq2*>(out)[i] = r;
         } break;
         case 5: {

@@ -291,6 +291,39 @@ def test_conditional_subtraction_tie_cases(eng):
     assert eng.field_op("fq_mul", a, b).tobytes() == c.fq_mul(a, b).tobytes()
 
 
+def test_mul_by_xi_quotient_estimate_boundaries(eng):
+    """fq2_mul_by_xi is two single-pass 9a +- b reductions with a 16-bit quotient estimate (fq_ptx.cuh).  Inputs are
+    built so that 9*a1 + a0 and 9*a0 + (q - a1) sit just below / at / above every multiple of q and at the edges of
+    the estimate's 2^242 granule; random and extreme elements on top.  Oracle: Fq2 multiplication by the element 9 + u."""
+    rng = np.random.default_rng(77)
+    Q = o.Q
+    pairs = []
+    for k in range(0, 11):
+        for d in (-2, -1, 0, 1, 2, (1 << 224) - 1, -(1 << 224), 1 << 242, -(1 << 242), (1 << 242) - 1):
+            tgt = k * Q + d
+            for _ in range(3):
+                hi = min(Q - 1, tgt // 9) if tgt >= 0 else -1
+                lo = max(0, -(-(tgt - (Q - 1)) // 9))
+                if hi < lo:
+                    continue
+                a9 = int(rng.integers(0, 1 << 62)) % (hi - lo + 1) + lo if hi - lo < (1 << 62) else lo + (util._rand_fq(rng) % (hi - lo + 1))
+                bb = tgt - 9 * a9
+                if not 0 <= bb < Q:
+                    continue
+                pairs.append((bb, a9))                        # c1 = 9*a1 + a0 = tgt
+                pairs.append((a9, (Q - bb) % Q))              # c0 = 9*a0 - a1 = tgt - q (mod q)
+    for v in (0, 1, Q - 1, Q - 2, (Q - 1) // 9, (Q - 1) // 9 + 1, Q // 2):
+        for w in (0, 1, Q - 1, Q // 3):
+            pairs.append((v, w))
+    pairs += [(util._rand_fq(rng), util._rand_fq(rng)) for _ in range(2000)]
+    a = np.frombuffer(util.fq_mont_bytes([x for p in pairs for x in p]), dtype=np.uint8).copy()
+    xi = np.tile(np.frombuffer(util.fq_mont_bytes([9, 1]), dtype=np.uint8), len(pairs))
+    got = eng.field_op("fq2_mul_by_xi", a)
+    assert got.tobytes() == c.fq2_mul(a, xi).tobytes()
+    exp = b"".join(util.fq_mont_bytes([(9 * x - y) % Q, (9 * y + x) % Q]) for x, y in pairs)
+    assert got.tobytes() == exp
+
+
 def test_fused_and_split_miller_paths_agree(eng):
     """Both Miller implementations (single fused kernel; affine -> line table -> Miller-from-table) give the
     same pre-final-exponentiation bytes as the oracle, including pairs with points at infinity."""
