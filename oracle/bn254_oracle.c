@@ -933,6 +933,15 @@ void orc_g2_from_compressed_many(const uint8_t *in, void *out, uint8_t *status, 
         ST(g2, out, i, res);
     }
 }
+/* test hook for the divrem restatement: 64 big-endian bytes -> quotient and remainder as little-endian u256 images */
+int orc_u512_divrem_q(const uint8_t *be, void *quot, void *rem) {
+    orc_init();
+    u256 q = {{0, 0}}, r;
+    int ok = u512_divrem_q(be, &q, &r);
+    memcpy(quot, &q, 32);
+    memcpy(rem, &r, 32);
+    return ok;
+}
 void orc_fq_sqrt_many(const void *a, void *out, uint8_t *some, size_t n) {
     orc_init();
     for (size_t i = 0; i < n; i++) { fq r = FQ_ZERO; some[i] = (uint8_t)fq_sqrt(LD(fq, a, i), &r); ST(fq, out, i, r); }

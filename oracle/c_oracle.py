@@ -262,6 +262,15 @@ def g2_from_compressed(enc, threads=0):
     return out, st
 
 
+def u512_divrem_q(value):
+    """U512::divrem by the Fq modulus (src/arith.rs:116-138) -> (quotient or None, remainder) as Python ints."""
+    be = np.frombuffer(int(value).to_bytes(64, "big"), dtype=np.uint8).copy()
+    quot, rem = np.zeros(32, dtype=np.uint8), np.zeros(32, dtype=np.uint8)
+    lib().orc_u512_divrem_q.restype = ctypes.c_int
+    ok = lib().orc_u512_divrem_q(_p(be), _p(quot), _p(rem))
+    return (int.from_bytes(quot.tobytes(), "little") if ok else None), int.from_bytes(rem.tobytes(), "little")
+
+
 fq_sqrt = _with_some("orc_fq_sqrt_many", FQ)
 fq2_sqrt = _with_some("orc_fq2_sqrt_many", 2 * FQ)
 

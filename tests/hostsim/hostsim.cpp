@@ -127,3 +127,10 @@ extern "C" void hs_g2_from_compressed(const unsigned char* enc, void* o, unsigne
         st(o, i, g);
     }
 }
+extern "C" int hs_u512_divrem_q(const unsigned char* be, void* quot, void* rem) {
+    uint32_t q[8], r[8];
+    bool ok = u512_divrem_q(q, r, be);
+    memcpy(quot, q, 32);
+    memcpy(rem, r, 32);
+    return ok ? 1 : 0;
+}

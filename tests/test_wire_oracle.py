@@ -181,3 +181,46 @@ def test_fast_subgroup_test_is_exact():
     assert res % r == 0 and gcd(res, cof) == 1
     lam = q % r                                   # psi acts on the subgroup as multiplication by q
     assert (u + 1 + u * lam + u * lam * lam - 2 * u * pow(lam, 3, r)) % r == 0
+
+
+def _u512(limbs64):
+    return sum(v << (64 * i) for i, v in enumerate(limbs64))
+
+
+def test_u512_divrem_reference_vectors():
+    """testing_divrem, src/arith.rs:588-785 (the cases taken modulo the Fq modulus), on the C oracle and on the
+    host build of the device routine; then random values against Python's divmod."""
+    import ctypes
+    from tests import hostsim
+    Q = o.Q
+
+    def dev(value):
+        be = np.frombuffer(int(value).to_bytes(64, "big"), dtype=np.uint8).copy()
+        quot, rem = np.zeros(32, dtype=np.uint8), np.zeros(32, dtype=np.uint8)
+        ok = hostsim.lib().hs_u512_divrem_q(be.ctypes.data_as(ctypes.c_void_p), quot.ctypes.data_as(ctypes.c_void_p),
+                                            rem.ctypes.data_as(ctypes.c_void_p))
+        return (int.from_bytes(quot.tobytes(), "little") if ok else None), int.from_bytes(rem.tobytes(), "little")
+
+    q2m1 = _u512([0x3b5458a2275d69b0, 0xa602072d09eac101, 0x4a50189c6d96cadc, 0x04689e957a1242c8,
+                  0x26edfa5c34c6b38d, 0xb00b855116375606, 0x599a6f7c0348d21c, 0x0925c4b8763cbf9c])
+    assert q2m1 == Q * Q - 1
+    cases = [
+        (Q, (1, 0)),                                    # modulus -> 1*q + 0
+        (q2m1, (Q - 1, Q - 1)),                         # q^2 - 1 -> (q-1) q + (q-1)
+        (q2m1 - 1, (Q - 1, Q - 2)),
+        ((1 << 512) - 1, (None, _u512([0xf32cfc5b538afa88, 0xb5e71911d44501fb, 0x47ab1eff0a417ff6, 0x06d89f71cab8351f]))),
+        (q2m1 + 1, (None, 0)),                          # q^2 fails
+        (q2m1 + 2, (None, 1)),
+    ]
+    for value, want in cases:
+        assert c.u512_divrem_q(value) == want, hex(value)
+        assert dev(value) == want, hex(value)
+    rng = np.random.default_rng(9)
+    for _ in range(100):                                # the reference's loop: c1*q + c0 round trip
+        c0, c1 = util._rand_fq(rng), util._rand_fq(rng)
+        assert c.u512_divrem_q(c1 * Q + c0) == (c1, c0) and dev(c1 * Q + c0) == (c1, c0)
+    for _ in range(100):
+        v = int.from_bytes(rng.bytes(64), "little") >> int(rng.integers(0, 260))
+        qq, rr = divmod(v, Q)
+        want = (qq if qq < Q else None, rr)
+        assert c.u512_divrem_q(v) == want and dev(v) == want
