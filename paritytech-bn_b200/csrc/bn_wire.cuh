@@ -120,6 +120,43 @@ BN_HD bool fq2_sqrt(Fq2& r, const Fq2& a) {
     }
     return true;
 }
+// Some square root of a in Fq2 (or false), with two Fq exponentiations instead of two Fq2 ones.  Used only by
+// G2::from_compressed, whose result does not depend on WHICH root sqrt returns: the tag picks between y and -y by
+// comparing them (src/lib.rs:515-523).  Norm method for q = 3 mod 4: n = a0^2 + a1^2 must be a residue in Fq (else
+// a is a non-square in Fq2); with s = sqrt(n), exactly one of t = (a0 + s)/2 and t - s is a residue when a1 != 0
+// (their product is -(a1/2)^2 and -1 is a non-residue).  r = t^((q-3)/4), x = r t satisfies x^2 = chi(t) t and
+// x r = chi(t), so 1/x = chi(t) r: no inversion.  chi(t) = 1: root (x, a1 r / 2); chi(t) = -1: root (-a1 r / 2, x).
+BN_HD bool fq2_sqrt_any(Fq2& r, const Fq2& a) {
+    uint32_t e[8];
+    exp_q_minus3_div4(e);
+    Fq n, t, w, s, x, h, one = fq_one();
+    if (fq_is_zero(a.c1)) {                         // a in Fq: sqrt(a0) or u * sqrt(-a0)
+        fq_pow_limbs(w, a.c0, e, 251);
+        fq_mul_ni(x, w, a.c0);
+        fq_mul_ni(t, x, x);
+        if (fq_is_zero(a.c0)) { r = fq2_zero(); return true; }
+        if (fq_eq(t, a.c0)) { r.c0 = x; fq_set_zero(r.c1); } else { fq_set_zero(r.c0); r.c1 = x; }
+        return true;
+    }
+    fq_mul_ni(n, a.c0, a.c0);
+    fq_mul_ni(t, a.c1, a.c1);
+    fq_add(n, n, t);
+    fq_pow_limbs(w, n, e, 251);
+    fq_mul_ni(s, w, n);                             // candidate sqrt(n)
+    fq_mul_ni(t, s, s);
+    if (!fq_eq(t, n)) return false;                 // the norm is a non-residue: no square root in Fq2
+    fq_add(t, a.c0, s);
+    fq_half(t, t);                                  // t = (a0 + s) / 2, non-zero because a1 != 0
+    fq_pow_limbs(w, t, e, 251);
+    fq_mul_ni(x, w, t);                             // x^2 = +-t
+    fq_mul_ni(h, a.c1, w);
+    fq_half(h, h);                                  // a1 r / 2
+    fq_mul_ni(n, x, x);
+    if (fq_eq(n, t)) { r.c0 = x; r.c1 = h; }
+    else { fq_neg(r.c0, h); r.c1 = x; }
+    (void)one;
+    return true;
+}
 // U512::from_slice + divrem(q), src/arith.rs:82-138: 64 big-endian bytes n -> (n / q, n % q).  false when
 // the quotient is not below q (the reference's None).  Bit-serial like the reference; the word index of the
 // dividend is static (outer loop unrolled), only the bit loop runs.
@@ -277,7 +314,7 @@ BN_HD uint8_t g2_decode(G2& out, const uint8_t* s, bool ref_ladder) {
     fq2_sqr(y2, a.x);
     fq2_mul(y2, y2, a.x);
     fq2_add(y2, y2, b);
-    if (!fq2_sqrt(y, y2)) return BN254_DECODE_NOT_MEMBER_;
+    if (!fq2_sqrt_any(y, y2)) return BN254_DECODE_NOT_MEMBER_;
     fq2_neg(yn, y);
     bool y_gt = fq2_u512_gt(y, yn);
     uint8_t tag = s[0];

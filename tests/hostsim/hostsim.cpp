@@ -109,6 +109,9 @@ extern "C" void hs_fq_sqrt(const void* a, void* o, unsigned char* some, size_t n
 extern "C" void hs_fq2_sqrt(const void* a, void* o, unsigned char* some, size_t n) {
     for (size_t i = 0; i < n; i++) { Fq2 x = ld<Fq2>(a, i), r = fq2_zero(); some[i] = fq2_sqrt(r, x); st(o, i, r); }
 }
+extern "C" void hs_fq2_sqrt_any(const void* a, void* o, unsigned char* some, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq2 x = ld<Fq2>(a, i), r = fq2_zero(); some[i] = fq2_sqrt_any(r, x); st(o, i, r); }
+}
 extern "C" void hs_g1_from_compressed(const unsigned char* enc, void* o, unsigned char* status, size_t n) {
     for (size_t i = 0; i < n; i++) {
         G1 g; memset(&g, 0, sizeof g);

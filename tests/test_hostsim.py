@@ -211,6 +211,21 @@ def test_wire_sqrt_and_validation_host_build():
     for i in range(len(pairs)):
         if some[i]:
             assert out[64 * i:64 * i + 64].tobytes() == ro[64 * i:64 * i + 64].tobytes()
+    # the decoder's root finder (norm method, any root): same existence answer, and the root squares back to a
+    more = [(rng.randrange(o.Q), rng.randrange(o.Q)) for _ in range(40)] + [(rng.randrange(o.Q), 0) for _ in range(8)] + [(0, rng.randrange(o.Q)) for _ in range(4)]
+    a = _mont([w for pr in pairs + more for w in pr])
+    npairs = len(pairs) + len(more)
+    out, some = np.empty_like(a), np.empty(npairs, dtype=np.uint8)
+    hostsim.lib().hs_fq2_sqrt_any(_p(a), _p(out), _p(some), ctypes.c_size_t(npairs))
+    ro, so = c.fq2_sqrt(a)
+    assert some.tobytes() == so.tobytes() and 0 < int(some.sum()) < npairs
+    sq = c.fq2_sqr(out)
+    for i in range(npairs):
+        if some[i]:
+            assert sq[64 * i:64 * i + 64].tobytes() == a[64 * i:64 * i + 64].tobytes()
+            root = o.fq_list_from_bytes(ro[64 * i:64 * i + 64].tobytes())
+            neg = util.fq_mont_bytes([(-root[0]) % o.Q, (-root[1]) % o.Q])
+            assert out[64 * i:64 * i + 64].tobytes() in (ro[64 * i:64 * i + 64].tobytes(), neg)
     g1 = util.affine_bytes([(1, 2), (1, 1), (1, 3), (0, 0)])
     st = np.empty(4, dtype=np.uint8)
     hostsim.lib().hs_g1_affine_check(_p(g1), _p(st), ctypes.c_size_t(4))
