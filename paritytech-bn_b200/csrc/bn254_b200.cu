@@ -38,6 +38,8 @@ struct bn254_ctx {
     size_t ws_bytes;
     int split_miller;  // 1: three-kernel Miller path (default), 0: fused single kernel (BN254_FUSED_MILLER=1)
     int split_fexp;    // 1: easy + hard final-exponentiation kernels (BN254_SPLIT_FEXP=1), 0: one kernel
+    int fexp_smem;     // hard part of the final exponentiation (BN254_FEXP_SMEM): 2 (default) = shared-memory slot file, one
+                       // phase-synchronised block per SM (k_final_exp_hard_sync); 1 = slot file, 64-thread blocks; 0 = local memory
     bool zerocopy_out; // pinned output buffers are written by the last kernel directly (BN254_ZEROCOPY_OUT=0 disables)
     bool subgroup_ref; // true: G2 order check with the reference's [r-1]P + P ladder (BN254_SUBGROUP_REF=1); false: psi test
 };
@@ -118,6 +120,13 @@ int bn254_ctx_create(int device, bn254_ctx** out) {
     c->io_bytes = 0;
     { const char* e = getenv("BN254_FUSED_MILLER"); c->split_miller = (e && e[0] == '1') ? 0 : 1; }
     { const char* e = getenv("BN254_SPLIT_FEXP"); c->split_fexp = (e && e[0] == '1') ? 1 : 0; }
+    { const char* e = getenv("BN254_FEXP_SMEM"); c->fexp_smem = e ? atoi(e) : 2; }
+    if (c->fexp_smem == 1) {
+        cudaFuncSetAttribute(k_final_exp_hard_s, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    } else if (c->fexp_smem == 2) {
+        cudaError_t ea = cudaFuncSetAttribute(k_final_exp_hard_sync, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_FEXP_BLOCK * BN_SLOT_STRIDE);
+        if (ea != cudaSuccess) { delete c; return fail(BN254_ERR_CUDA, "cudaFuncSetAttribute(k_final_exp_hard_sync)", ea); }
+    }
     { const char* e = getenv("BN254_SUBGROUP_REF"); c->subgroup_ref = (e && e[0] == '1'); }
     { const char* e = getenv("BN254_ZEROCOPY_OUT"); c->zerocopy_out = !(e && e[0] == '0'); }
     e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
@@ -159,7 +168,7 @@ static int ctx_workspace(bn254_ctx* ctx, size_t bytes, void** out) {
 }
 // final exponentiation of n values (in place allowed): single kernel, or easy + hard kernels
 static int final_exp_dev(bn254_ctx* ctx, const Fq12* d_in, Fq12* d_out, uint8_t* d_some, uint8_t* d_is_one, size_t n) {
-    if (!ctx->split_fexp) {
+    if (!ctx->split_fexp && !ctx->fexp_smem) {
         LAUNCH(ctx, k_final_exp_many, n, d_in, d_out, d_some, d_is_one, n);
         return 0;
     }
@@ -170,6 +179,19 @@ static int final_exp_dev(bn254_ctx* ctx, const Fq12* d_in, Fq12* d_out, uint8_t*
     Fq12* t = (Fq12*)ws;
     uint8_t* flags = (uint8_t*)ws + vals;
     LAUNCH(ctx, k_final_exp_easy, n, d_in, t, flags, n);
+    if (ctx->fexp_smem == 2) {
+        unsigned g = (unsigned)((n + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK);
+        k_final_exp_hard_sync<<<g, BN_FEXP_BLOCK, BN_FEXP_BLOCK * BN_SLOT_STRIDE, ctx->stream>>>((const Fq12*)t, (const uint8_t*)flags, d_out, d_some, d_is_one, n);
+        ctx->launches.fetch_add(1);
+        CU(cudaGetLastError());
+        return 0;
+    }
+    if (ctx->fexp_smem) {
+        k_final_exp_hard_s<<<grid_for(n), BN_BLOCK, BN_BLOCK * BN_SLOT_STRIDE, ctx->stream>>>((const Fq12*)t, (const uint8_t*)flags, d_out, d_some, d_is_one, n);
+        ctx->launches.fetch_add(1);
+        CU(cudaGetLastError());
+        return 0;
+    }
     LAUNCH(ctx, k_final_exp_hard, n, (const Fq12*)t, (const uint8_t*)flags, d_out, d_some, d_is_one, n);
     return 0;
 }

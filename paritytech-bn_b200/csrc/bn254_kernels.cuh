@@ -4,6 +4,7 @@
 #pragma once
 #include "bn_curve.cuh"
 #include "bn_wire.cuh"
+#include "bn_slots.cuh"
 
 namespace bn {
 
@@ -109,6 +110,45 @@ BN_KERNEL_FEXP k_final_exp_hard(const Fq12* __restrict__ in, const uint8_t* __re
     bool s = some_in[i] != 0;
     Fq12 f = in[i], r;
     if (s) fq12_final_exp_last_chunk(r, f); else r = fq12_zero();
+    if (out) out[i] = r;
+    if (some) some[i] = s ? 1 : 0;
+    if (is_one) {
+        Fq12 one = fq12_one();
+        is_one[i] = fq12_eq(r, one) ? 1 : 0;
+    }
+}
+
+// hard part on the shared-memory slot file (bn_slots.cuh): launched with BN_BLOCK * BN_SLOT_STRIDE bytes of dynamic
+// shared memory, 7 blocks per SM
+__global__ void __launch_bounds__(BN_BLOCK, 7) k_final_exp_hard_s(const Fq12* __restrict__ in, const uint8_t* __restrict__ some_in,
+                           Fq12* __restrict__ out, uint8_t* __restrict__ some, uint8_t* __restrict__ is_one, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    bool s = some_in[i] != 0;
+    Fq12 f = in[i], r;
+    if (s) s_fq12_final_exp_last_chunk<false>(r, f, s_base()); else r = fq12_zero();
+    if (out) out[i] = r;
+    if (some) some[i] = s ? 1 : 0;
+    if (is_one) {
+        Fq12 one = fq12_one();
+        is_one[i] = fq12_eq(r, one) ? 1 : 0;
+    }
+}
+
+// same, one block of BN_FEXP_BLOCK threads per SM with phase barriers (bn_slots.cuh, s_phase): threads past n run the
+// schedule on zeros so that every barrier is reached by the whole block
+#ifndef BN_FEXP_BLOCK
+#define BN_FEXP_BLOCK 448
+#endif
+__global__ void __launch_bounds__(BN_FEXP_BLOCK, 1) k_final_exp_hard_sync(const Fq12* __restrict__ in, const uint8_t* __restrict__ some_in,
+                           Fq12* __restrict__ out, uint8_t* __restrict__ some, uint8_t* __restrict__ is_one, size_t n) {
+    size_t i = gtid();
+    bool live = i < n;
+    bool s = live && some_in[i] != 0;
+    Fq12 f, r;
+    if (s) f = in[i]; else f = fq12_zero();
+    s_fq12_final_exp_last_chunk<true>(r, f, s_base());
+    if (!live) return;
     if (out) out[i] = r;
     if (some) some[i] = s ? 1 : 0;
     if (is_one) {

@@ -1,0 +1,320 @@
+// Shared-memory slot file for the hot Fq12 loops (device only).
+//
+// Measured on B200 (profiles/r01_ncu_l1_l2_traffic.md): the L1 is write-through, so every Fq2 result that an
+// out-of-line body stores to local memory travels to the L2 (63 GB per 2^16 final exponentiations, 5 TB/s), and
+// with 14 warps per SM sharing ~200 KB of L1 the consumer of that value usually misses (first use of a loaded
+// operand: ~400 clk, 60 % of the samples of fq2_add/fq2_sub).  Shared memory is the same SRAM without either
+// problem: stores stay on chip and loads always hit.
+//
+// Each thread owns BN_NSLOTS Fq2 slots (64 B each) in shared memory at a per-thread stride of 464 B = 29 x 16 B:
+// an odd number of 16-byte units, so the 8 threads of a quarter-warp hit 8 different bank groups on every 128-bit
+// access (conflict-free), and 7 blocks x 64 threads x 464 B = 208 KB fit one SM.  All Fq2 arithmetic of the hot
+// loops (cyclotomic squaring and Fq12 multiplication of the final exponentiation's hard part,
+// src/fields/fq12.rs:75-105, :198-266, :316-328) runs slot to slot through explicit ld.shared/st.shared bodies;
+// the Fq12 values themselves stay in local memory and are touched only by coefficient fetches and result stores.
+// Same field elements as the local-memory path in bn_tower.cuh, hence the same bytes.
+#pragma once
+#include "bn_tower.cuh"
+
+#if defined(__CUDACC__)
+namespace bn {
+
+#define BN_NSLOTS 7
+#define BN_SLOT_STRIDE (BN_NSLOTS * 64 + 16)
+typedef uint32_t sp;   // shared-window byte address of one Fq2 slot
+
+__device__ __forceinline__ uint4 lds128(sp a) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts128(sp a, uint4 v) {
+    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ Fq2 s_ld(sp a) {
+    uint4 w0 = lds128(a), w1 = lds128(a + 16), w2 = lds128(a + 32), w3 = lds128(a + 48);
+    Fq2 r;
+    r.c0.v[0] = w0.x; r.c0.v[1] = w0.y; r.c0.v[2] = w0.z; r.c0.v[3] = w0.w;
+    r.c0.v[4] = w1.x; r.c0.v[5] = w1.y; r.c0.v[6] = w1.z; r.c0.v[7] = w1.w;
+    r.c1.v[0] = w2.x; r.c1.v[1] = w2.y; r.c1.v[2] = w2.z; r.c1.v[3] = w2.w;
+    r.c1.v[4] = w3.x; r.c1.v[5] = w3.y; r.c1.v[6] = w3.z; r.c1.v[7] = w3.w;
+    return r;
+}
+__device__ __forceinline__ void s_st(sp a, const Fq2& v) {
+    sts128(a, make_uint4(v.c0.v[0], v.c0.v[1], v.c0.v[2], v.c0.v[3]));
+    sts128(a + 16, make_uint4(v.c0.v[4], v.c0.v[5], v.c0.v[6], v.c0.v[7]));
+    sts128(a + 32, make_uint4(v.c1.v[0], v.c1.v[1], v.c1.v[2], v.c1.v[3]));
+    sts128(a + 48, make_uint4(v.c1.v[4], v.c1.v[5], v.c1.v[6], v.c1.v[7]));
+}
+extern __shared__ uint4 bn_slot_mem[];
+__device__ __forceinline__ sp s_base() {
+    return (sp)__cvta_generic_to_shared(bn_slot_mem) + threadIdx.x * BN_SLOT_STRIDE;
+}
+
+// ---- slot-to-slot Fq2 bodies (r may alias a or b) -------------------------------------------------------------
+__device__ __noinline__ void s_mul(sp r, sp a, sp b) { Fq2 x = s_ld(a), y = s_ld(b), z; fq2_mul_inl(z, x, y); s_st(r, z); }
+__device__ __noinline__ void s_add(sp r, sp a, sp b) { Fq2 x = s_ld(a), y = s_ld(b), z; fq_add(z.c0, x.c0, y.c0); fq_add(z.c1, x.c1, y.c1); s_st(r, z); }
+__device__ __noinline__ void s_sub(sp r, sp a, sp b) { Fq2 x = s_ld(a), y = s_ld(b), z; fq_sub(z.c0, x.c0, y.c0); fq_sub(z.c1, x.c1, y.c1); s_st(r, z); }
+__device__ __noinline__ void s_dbl(sp r, sp a) { Fq2 x = s_ld(a), z; fq_dbl(z.c0, x.c0); fq_dbl(z.c1, x.c1); s_st(r, z); }
+__device__ __noinline__ void s_xi(sp r, sp a) {
+    Fq2 x = s_ld(a), n;
+    fq_lin9<true>(n.c0, x.c0, x.c1);
+    fq_lin9<false>(n.c1, x.c1, x.c0);
+    s_st(r, n);
+}
+// coefficient fetch from local memory: slot = p (mode 0), p + q (1), p - q (2)
+__device__ __noinline__ void s_fetch(sp r, const Fq2& p, const Fq2& q, int mode) {
+    Fq2 x = fq2_ld(p);
+    if (mode != 0) {
+        Fq2 y = fq2_ld(q), z;
+        if (mode == 1) { fq_add(z.c0, x.c0, y.c0); fq_add(z.c1, x.c1, y.c1); }
+        else { fq_sub(z.c0, x.c0, y.c0); fq_sub(z.c1, x.c1, y.c1); }
+        x = z;
+    }
+    s_st(r, x);
+}
+__device__ __forceinline__ void s_in(sp r, const Fq2& p) { s_st(r, fq2_ld(p)); }
+__device__ __forceinline__ void s_out(Fq2& p, sp a) { fq2_st(p, s_ld(a)); }
+
+__device__ __forceinline__ const Fq2& f12c(const Fq12& a, int i) { return reinterpret_cast<const Fq2*>(&a)[i]; }
+__device__ __forceinline__ Fq2& f12c(Fq12& a, int i) { return reinterpret_cast<Fq2*>(&a)[i]; }
+__device__ __forceinline__ const Fq2& f6c(const Fq6& a, int i) { return reinterpret_cast<const Fq2*>(&a)[i]; }
+__device__ __forceinline__ Fq2& f6c(Fq6& a, int i) { return reinterpret_cast<Fq2*>(&a)[i]; }
+
+// ---- Granger-Scott squaring, one coefficient pair per call (value of src/fields/fq12.rs:198-247) --------------
+// Fq12 as six Fq2: index 0..5 = c0.c0, c0.c1, c0.c2, c1.c0, c1.c1, c1.c2 = the reference's z0, z4, z3, z2, z1, z5.
+//   p = 0: (t0, t1) = sqr4(z0, z1): z0' = 3 t0 - 2 z0, z1' = 3 t1 + 2 z1
+//   p = 1: (t2, t3) = sqr4(z2, z3): z4' = 3 t2 - 2 z4, z5' = 3 t3 + 2 z5
+//   p = 2: (t4, t5) = sqr4(z4, z5): z3' = 3 t4 - 2 z3, z2' = 3 xi t5 + 2 z2
+// r must not overlap a.
+#ifndef BN_CYC_FUSED
+#define BN_CYC_FUSED 1
+#endif
+#if BN_CYC_FUSED
+// Two register-resident stages around the two products of one pair: the additive work of the Fq4 squaring and of
+// the 3t -+ 2z outputs never leaves registers, and the pair costs 4 calls instead of 17.
+// pre: slots A = a, B = b, S = a + b, T = a + xi b (operands read from local memory)
+__device__ __noinline__ void s_cyc_pre(sp base, const Fq2& pa, const Fq2& pb) {
+    Fq2 a = fq2_ld(pa), b = fq2_ld(pb), s, t;
+    s_st(base, a); s_st(base + 64, b);
+    fq_add(s.c0, a.c0, b.c0); fq_add(s.c1, a.c1, b.c1);
+    s_st(base + 320, s);
+    fq_lin9<true>(t.c0, b.c0, b.c1);
+    fq_lin9<false>(t.c1, b.c1, b.c0);
+    fq_add(t.c0, t.c0, a.c0); fq_add(t.c1, t.c1, a.c1);
+    s_st(base + 384, t);
+}
+// out = 3 t - 2 z (minus) or 3 t + 2 z, every step reduced
+__device__ __forceinline__ void fq2_3t2z(Fq2& out, const Fq2& t, const Fq2& z, bool plus) {
+    Fq2 d;
+    if (plus) { fq_add(d.c0, t.c0, z.c0); fq_add(d.c1, t.c1, z.c1); }
+    else { fq_sub(d.c0, t.c0, z.c0); fq_sub(d.c1, t.c1, z.c1); }
+    fq_dbl(d.c0, d.c0); fq_dbl(d.c1, d.c1);
+    fq_add(out.c0, d.c0, t.c0); fq_add(out.c1, d.c1, t.c1);
+}
+// post: with S = (a + b)(a + xi b) and TMP = a b in the slots: ta = S - TMP - xi TMP, tb = 2 TMP (times xi if xi_d);
+// out_c = 3 ta - 2 zc, out_d = 3 tb + 2 zd written to local memory
+__device__ __noinline__ void s_cyc_post(Fq2& out_c, Fq2& out_d, const Fq2& zc, const Fq2& zd, sp base, bool xi_d) {
+    Fq2 m = s_ld(base + 256), s = s_ld(base + 320), u, z;
+    fq_lin9<true>(u.c0, m.c0, m.c1);
+    fq_lin9<false>(u.c1, m.c1, m.c0);
+    fq_sub(s.c0, s.c0, m.c0); fq_sub(s.c1, s.c1, m.c1);
+    fq_sub(s.c0, s.c0, u.c0); fq_sub(s.c1, s.c1, u.c1);      // ta
+    z = fq2_ld(zc);
+    fq2_3t2z(z, s, z, false);
+    fq2_st(out_c, z);
+    if (xi_d) { fq_dbl(m.c0, u.c0); fq_dbl(m.c1, u.c1); }    // xi (2 TMP) = 2 (xi TMP)
+    else { fq_dbl(m.c0, m.c0); fq_dbl(m.c1, m.c1); }         // tb
+    z = fq2_ld(zd);
+    fq2_3t2z(z, m, z, true);
+    fq2_st(out_d, z);
+}
+__device__ __forceinline__ void s_cyc_pair(Fq12& r, const Fq12& a, int p, sp base) {
+    const int ia = (p == 0) ? 0 : (p == 1) ? 3 : 1;
+    const int ib = (p == 0) ? 4 : (p == 1) ? 2 : 5;
+    const int ic = p;
+    const int id = (p == 0) ? 4 : (p == 1) ? 5 : 3;
+    s_cyc_pre(base, f12c(a, ia), f12c(a, ib));
+    s_mul(base + 256, base, base + 64);             // TMP = a b
+    s_mul(base + 320, base + 320, base + 384);      // S = (a + b)(a + xi b)
+    s_cyc_post(f12c(r, ic), f12c(r, id), f12c(a, ic), f12c(a, id), base, p == 2);
+}
+#else
+__device__ __noinline__ void s_cyc_pair(Fq12& r, const Fq12& a, int p, sp base) {
+    const int ia = (p == 0) ? 0 : (p == 1) ? 3 : 1;
+    const int ib = (p == 0) ? 4 : (p == 1) ? 2 : 5;
+    const int ic = p;
+    const int id = (p == 0) ? 4 : (p == 1) ? 5 : 3;
+    const sp A = base, B = base + 64, C = base + 128, D = base + 192, TMP = base + 256, S = base + 320, T = base + 384;
+    s_in(A, f12c(a, ia)); s_in(B, f12c(a, ib)); s_in(C, f12c(a, ic)); s_in(D, f12c(a, id));
+    s_mul(TMP, A, B);                 // a b
+    s_xi(T, B); s_add(T, T, A);       // a + xi b
+    s_add(S, A, B);
+    s_mul(S, S, T);                   // (a + b)(a + xi b)
+    s_sub(S, S, TMP);
+    s_xi(T, TMP);
+    s_sub(S, S, T);                   // a^2 + xi b^2
+    s_dbl(TMP, TMP);                  // 2 a b
+    if (p == 2) s_xi(TMP, TMP);
+    s_sub(C, S, C); s_dbl(C, C); s_add(C, C, S);
+    s_add(D, TMP, D); s_dbl(D, D); s_add(D, D, TMP);
+    s_out(f12c(r, ic), C); s_out(f12c(r, id), D);
+}
+#endif
+__device__ __forceinline__ void s_cyclotomic_sqr_na(Fq12& r, const Fq12& a, sp base) {
+    s_cyc_pair(r, a, 0, base);
+    s_cyc_pair(r, a, 1, base);
+    s_cyc_pair(r, a, 2, base);
+}
+
+// ---- Fq6 product on slots (value of src/fields/fq6.rs:194-208) -------------------------------------------------
+#define BN_SKIP 0xffffffffu
+// one side of a Karatsuba stage: slots dI <- p_i, dJ <- p_j (skipped when BN_SKIP), dS <- p_i + p_j; operands in local memory
+__device__ __noinline__ void s_prep1(const Fq2& pi, const Fq2& pj, sp dI, sp dJ, sp dS) {
+    Fq2 x = fq2_ld(pi), y = fq2_ld(pj), s;
+    if (dI != BN_SKIP) s_st(dI, x);
+    if (dJ != BN_SKIP) s_st(dJ, y);
+    fq_add(s.c0, x.c0, y.c0); fq_add(s.c1, x.c1, y.c1);
+    s_st(dS, s);
+}
+// one output coefficient: t = Q - Va - Vb; kind 0: xi t + Vc, kind 1: t + xi Vc, kind 2: t + Vc; then minus (aa + bb) for
+// post = 1, minus (aa - bb) for post = 2 (the Fq12-level Karatsuba correction, operands in local memory); result to local memory
+__device__ __noinline__ void s_f6_out(Fq2& out, sp Q, sp Va, sp Vb, sp Vc, int kind, const Fq2& aa, const Fq2& bb, int post) {
+    Fq2 t = s_ld(Q), v = s_ld(Va), w = s_ld(Vc), x, y;
+    fq_sub(t.c0, t.c0, v.c0); fq_sub(t.c1, t.c1, v.c1);
+    v = s_ld(Vb);
+    fq_sub(t.c0, t.c0, v.c0); fq_sub(t.c1, t.c1, v.c1);
+    if (kind == 0) { x = t; y = w; } else { x = w; y = t; }
+    if (kind != 2) {
+        Fq2 n;
+        fq_lin9<true>(n.c0, x.c0, x.c1);
+        fq_lin9<false>(n.c1, x.c1, x.c0);
+        x = n;
+    }
+    fq_add(t.c0, x.c0, y.c0); fq_add(t.c1, x.c1, y.c1);
+    if (post) {
+        x = fq2_ld(aa); y = fq2_ld(bb);
+        if (post == 1) { fq_add(x.c0, x.c0, y.c0); fq_add(x.c1, x.c1, y.c1); }
+        else { fq_sub(x.c0, x.c0, y.c0); fq_sub(x.c1, x.c1, y.c1); }
+        fq_sub(t.c0, t.c0, x.c0); fq_sub(t.c1, t.c1, x.c1);
+    }
+    fq2_st(out, t);
+}
+// out = a + b, a - b (neg), a + xi b, a - xi b; local memory to local memory (Fq6/Fq12-level Karatsuba sums)
+__device__ __noinline__ void l_lin(Fq2& out, const Fq2& a, const Fq2& b, bool neg, bool xi) {
+    Fq2 x = fq2_ld(a), y = fq2_ld(b);
+    if (xi) {
+        Fq2 n;
+        fq_lin9<true>(n.c0, y.c0, y.c1);
+        fq_lin9<false>(n.c1, y.c1, y.c0);
+        y = n;
+    }
+    if (neg) { fq_sub(x.c0, x.c0, y.c0); fq_sub(x.c1, x.c1, y.c1); }
+    else { fq_add(x.c0, x.c0, y.c0); fq_add(x.c1, x.c1, y.c1); }
+    fq2_st(out, x);
+}
+// out = a * b, operands and result in local memory, out not overlapping them.  post != 0 finishes an Fq12 Karatsuba product
+// in the same pass: out_i = (a b)_i - (aa_i + bb_i) for post = 1, (a b)_i - (aa_i - bb_i) for post = 2.
+// Karatsuba (6 products) in three stages of 3 + 2 + 1 products on the 7 slots; 15 calls.
+__device__ __noinline__ void s_fq6_mul(Fq6& out, const Fq6& a, const Fq6& b, const Fq6& aa, const Fq6& bb, int post, sp base) {
+    const sp s0 = base, s1 = base + 64, s2 = base + 128, s3 = base + 192, s4 = base + 256, s5 = base + 320, s6 = base + 384;
+    s_prep1(a.c0, a.c1, s0, s2, s4);
+    s_prep1(b.c0, b.c1, s1, s3, s5);
+    s_mul(s0, s0, s1);                       // v0 = a0 b0
+    s_mul(s2, s2, s3);                       // v1 = a1 b1
+    s_mul(s4, s4, s5);                       // (a0 + a1)(b0 + b1)
+    s_prep1(a.c1, a.c2, BN_SKIP, s1, s5);
+    s_prep1(b.c1, b.c2, BN_SKIP, s3, s6);
+    s_mul(s1, s1, s3);                       // v2 = a2 b2
+    s_mul(s5, s5, s6);                       // (a1 + a2)(b1 + b2)
+    s_prep1(a.c0, a.c2, BN_SKIP, BN_SKIP, s3);
+    s_prep1(b.c0, b.c2, BN_SKIP, BN_SKIP, s6);
+    s_mul(s3, s3, s6);                       // (a0 + a2)(b0 + b2)
+    s_f6_out(out.c0, s5, s2, s1, s0, 0, aa.c0, bb.c0, post);    // v0 + xi ((a1+a2)(b1+b2) - v1 - v2)
+    s_f6_out(out.c1, s4, s0, s2, s1, 1, aa.c1, bb.c1, post);    // (a0+a1)(b0+b1) - v0 - v1 + xi v2
+    s_f6_out(out.c2, s3, s0, s1, s2, 2, aa.c2, bb.c2, post);    // (a0+a2)(b0+b2) - v0 - v2 + v1
+}
+// r = a * b (conj_b: a * conj(b)); value of src/fields/fq12.rs:316-328.  r must not overlap a or b.
+__device__ __noinline__ void s_fq12_mul_na(Fq12& r, const Fq12& a, const Fq12& b, bool conj_b, sp base) {
+    Fq6 aa, bb, sb;
+    s_fq6_mul(aa, a.c0, b.c0, aa, aa, 0, base);
+    s_fq6_mul(bb, a.c1, b.c1, bb, bb, 0, base);
+    // r.c0 doubles as the buffer of a0 + a1; c1 = (a0 + a1)(b0 +- b1) - (aa +- bb)
+    l_lin(r.c0.c0, a.c0.c0, a.c1.c0, false, false); l_lin(r.c0.c1, a.c0.c1, a.c1.c1, false, false); l_lin(r.c0.c2, a.c0.c2, a.c1.c2, false, false);
+    l_lin(sb.c0, b.c0.c0, b.c1.c0, conj_b, false); l_lin(sb.c1, b.c0.c1, b.c1.c1, conj_b, false); l_lin(sb.c2, b.c0.c2, b.c1.c2, conj_b, false);
+    s_fq6_mul(r.c1, r.c0, sb, aa, bb, conj_b ? 2 : 1, base);
+    // c0 = aa +- v bb, v (b0, b1, b2) = (xi b2, b0, b1)
+    l_lin(r.c0.c0, aa.c0, bb.c2, conj_b, true);
+    l_lin(r.c0.c1, aa.c1, bb.c0, conj_b, false);
+    l_lin(r.c0.c2, aa.c2, bb.c1, conj_b, false);
+}
+
+// conj(a^u): same width-4 signed-window chain as fq12_exp_by_neg_z (bn_tower.cuh), on the slot bodies
+// SYNC: the whole block (one per SM) changes between the squaring code and the multiplication code together, so the
+// hot SASS of either phase -- not their union -- has to fit the 32 KB instruction cache (every thread runs the same
+// fixed schedule: the exponent is a constant).
+template <bool SYNC> __device__ __forceinline__ void s_phase() { if (SYNC) __syncthreads(); }
+template <bool SYNC> __device__ __noinline__ void s_fq12_exp_by_neg_z(Fq12& r, const Fq12& a, sp base) {
+    Fq12 a3, a5, a7, buf0, buf1;
+    s_cyclotomic_sqr_na(buf0, a, base);
+    s_phase<SYNC>();
+    s_fq12_mul_na(a3, buf0, a, false, base);
+    s_fq12_mul_na(a5, buf0, a3, false, base);
+    s_fq12_mul_na(a7, buf0, a5, false, base);
+    s_phase<SYNC>();
+    bool in0 = true;
+    for (int i = 61; i >= 0; i--) {
+        if (i != 61) {
+            if (in0) s_cyclotomic_sqr_na(buf1, buf0, base); else s_cyclotomic_sqr_na(buf0, buf1, base);
+            in0 = !in0;
+        }
+        if ((BN_U_WNAF4_NZ >> i) & 1) {
+            bool neg = ((BN_U_WNAF4_NEG >> i) & 1) != 0;
+            int idx = (int)((BN_U_WNAF4_I0 >> i) & 1) | ((int)((BN_U_WNAF4_I1 >> i) & 1) << 1);
+            s_phase<SYNC>();
+            if (idx == 0) { if (in0) s_fq12_mul_na(buf1, buf0, a, neg, base); else s_fq12_mul_na(buf0, buf1, a, neg, base); }
+            else if (idx == 1) { if (in0) s_fq12_mul_na(buf1, buf0, a3, neg, base); else s_fq12_mul_na(buf0, buf1, a3, neg, base); }
+            else if (idx == 2) { if (in0) s_fq12_mul_na(buf1, buf0, a5, neg, base); else s_fq12_mul_na(buf0, buf1, a5, neg, base); }
+            else { if (in0) s_fq12_mul_na(buf1, buf0, a7, neg, base); else s_fq12_mul_na(buf0, buf1, a7, neg, base); }
+            s_phase<SYNC>();
+            in0 = !in0;
+        }
+    }
+    if (in0) fq12_conj(r, buf0); else fq12_conj(r, buf1);
+}
+// hard part, the reference's addition chain (src/fields/fq12.rs:75-105, step names in the comments); every product
+// writes a buffer that is dead at that point, so the non-aliasing slot bodies apply.  out must not overlap x.
+template <bool SYNC> __device__ __noinline__ void s_fq12_final_exp_last_chunk(Fq12& out, const Fq12& x, sp base) {
+    Fq12 a, b, c, d, e, f, g;
+    s_fq12_exp_by_neg_z<SYNC>(a, x, base);    // a
+    s_cyclotomic_sqr_na(b, a, base);          // b
+    s_cyclotomic_sqr_na(c, b, base);          // c
+    s_phase<SYNC>();
+    s_fq12_mul_na(d, c, b, false, base);      // d
+    s_phase<SYNC>();
+    s_fq12_exp_by_neg_z<SYNC>(e, d, base);    // e
+    s_cyclotomic_sqr_na(f, e, base);          // f
+    s_fq12_exp_by_neg_z<SYNC>(g, f, base);    // g
+    s_phase<SYNC>();
+    s_fq12_mul_na(a, e, g, true, base);       // j = conj(g) e
+    s_fq12_mul_na(c, a, d, true, base);       // k = j conj(d)
+    s_fq12_mul_na(f, c, b, false, base);      // l = k b
+    s_fq12_mul_na(a, c, e, false, base);      // m = k e
+    s_fq12_mul_na(g, x, a, false, base);      // n = x m
+    s_phase<SYNC>();
+    fq12_frobenius(a, f, 1);                  // o
+    s_phase<SYNC>();
+    s_fq12_mul_na(b, a, g, false, base);      // p = o n
+    s_phase<SYNC>();
+    fq12_frobenius(a, c, 2);                  // q
+    s_phase<SYNC>();
+    s_fq12_mul_na(g, a, b, false, base);      // r = q p
+    s_fq12_mul_na(a, f, x, true, base);       // t = conj(x) l
+    s_phase<SYNC>();
+    fq12_frobenius(b, a, 3);                  // u
+    s_phase<SYNC>();
+    s_fq12_mul_na(out, b, g, false, base);    // v = u r
+}
+
+}  // namespace bn
+#endif
