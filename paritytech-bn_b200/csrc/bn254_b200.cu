@@ -38,6 +38,7 @@ struct bn254_ctx {
     size_t ws_bytes;
     int split_miller;  // 1: three-kernel Miller path (default), 0: fused single kernel (BN254_FUSED_MILLER=1)
     int split_fexp;    // 1: easy + hard final-exponentiation kernels (BN254_SPLIT_FEXP=1), 0: one kernel
+    int miller_smem;   // 1 (default): Miller loop from the table on the slot file (k_miller_table_sync; BN254_MILLER_SMEM=0: local memory)
     int fexp_smem;     // hard part of the final exponentiation (BN254_FEXP_SMEM): 2 (default) = shared-memory slot file, one
                        // phase-synchronised block per SM (k_final_exp_hard_sync); 1 = slot file, 64-thread blocks; 0 = local memory
     bool zerocopy_out; // pinned output buffers are written by the last kernel directly (BN254_ZEROCOPY_OUT=0 disables)
@@ -121,6 +122,11 @@ int bn254_ctx_create(int device, bn254_ctx** out) {
     { const char* e = getenv("BN254_FUSED_MILLER"); c->split_miller = (e && e[0] == '1') ? 0 : 1; }
     { const char* e = getenv("BN254_SPLIT_FEXP"); c->split_fexp = (e && e[0] == '1') ? 1 : 0; }
     { const char* e = getenv("BN254_FEXP_SMEM"); c->fexp_smem = e ? atoi(e) : 2; }
+    { const char* e = getenv("BN254_MILLER_SMEM"); c->miller_smem = e ? atoi(e) : 1; }
+    if (c->miller_smem) {
+        cudaError_t ea = cudaFuncSetAttribute(k_miller_table_sync, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_FEXP_BLOCK * BN_SLOT_STRIDE);
+        if (ea != cudaSuccess) { delete c; return fail(BN254_ERR_CUDA, "cudaFuncSetAttribute(k_miller_table_sync)", ea); }
+    }
     if (c->fexp_smem == 1) {
         cudaFuncSetAttribute(k_final_exp_hard_s, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
     } else if (c->fexp_smem == 2) {
@@ -209,6 +215,18 @@ static int ctx_io(bn254_ctx* ctx, const size_t* sizes, int count, void** out) {
     for (int i = 0; i < count; i++) { out[i] = p; p += (sizes[i] + 255) & ~(size_t)255; }
     return 0;
 }
+// Miller loop of m pairs from their line tables: slot-file kernel (one 448-thread block per SM) or the local-memory kernel
+static int miller_table_launch(bn254_ctx* ctx, const AffG1* pa, const uint8_t* ok, const uint4* tab, Fq12* f, uint8_t* ok_out, size_t m) {
+    if (ctx->miller_smem) {
+        unsigned g = (unsigned)((m + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK);
+        k_miller_table_sync<<<g, BN_FEXP_BLOCK, BN_FEXP_BLOCK * BN_SLOT_STRIDE, ctx->stream>>>(pa, ok, tab, f, ok_out, m);
+        ctx->launches.fetch_add(1);
+        CU(cudaGetLastError());
+        return 0;
+    }
+    LAUNCH(ctx, k_miller_table_affine, m, pa, ok, tab, f, ok_out, m);
+    return 0;
+}
 static const size_t MILLER_CHUNK = (size_t)1 << 17;   // pairings per table chunk (2.2 GB of line coefficients)
 // Miller values of n independent pairs (fused single kernel, or affine -> line table -> Miller from table)
 static int miller_many_dev(bn254_ctx* ctx, const G2* d_g2, const G1* d_g1, Fq12* d_f, uint8_t* d_ok, size_t n) {
@@ -229,7 +247,7 @@ static int miller_many_dev(bn254_ctx* ctx, const G2* d_g2, const G1* d_g1, Fq12*
         size_t m = n - lo < chunk ? n - lo : chunk;
         LAUNCH(ctx, k_pairs_to_affine, m, d_g2 + lo, d_g1 + lo, qa, pa, ok, m);
         LAUNCH(ctx, k_g2_lines_affine, m, (const AffG2*)qa, (const uint8_t*)ok, tab, m, (size_t)1);
-        LAUNCH(ctx, k_miller_table_affine, m, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tab, d_f + lo, d_ok ? d_ok + lo : (uint8_t*)nullptr, m);
+        TRY(miller_table_launch(ctx, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tab, d_f + lo, d_ok ? d_ok + lo : (uint8_t*)nullptr, m));
     }
     return 0;
 }
@@ -282,7 +300,7 @@ int bn254_pairing_many_dev_timed(bn254_ctx* ctx, const void* d_g1, const void* d
                 CU(cudaEventRecord(ev[1], ctx->stream));
                 LAUNCH(ctx, k_g2_lines_affine, m, (const AffG2*)qa, (const uint8_t*)ok, tab, m, (size_t)1);
                 CU(cudaEventRecord(ev[2], ctx->stream));
-                LAUNCH(ctx, k_miller_table_affine, m, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tab, f + lo, (uint8_t*)nullptr, m);
+                TRY(miller_table_launch(ctx, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tab, f + lo, (uint8_t*)nullptr, m));
                 CU(cudaEventRecord(ev[3], ctx->stream));
                 CU(cudaEventSynchronize(ev[3]));
                 for (int i = 0; i < 3; i++) { float t; CU(cudaEventElapsedTime(&t, ev[i], ev[i + 1])); ms[i] += t; }

@@ -157,6 +157,42 @@ __global__ void __launch_bounds__(BN_FEXP_BLOCK, 1) k_final_exp_hard_sync(const 
     }
 }
 
+// Miller loop from the line table on the slot file, one phase-synchronised block per SM: the squaring code and the
+// line-multiplication code alternate under block barriers so that each fits the instruction cache on its own
+// (G2Precomp::miller_loop, src/groups/mod.rs:580-606; same values as k_miller_table_affine).
+__global__ void __launch_bounds__(BN_FEXP_BLOCK, 1) k_miller_table_sync(const AffG1* __restrict__ pa_in, const uint8_t* __restrict__ ok_in,
+                                const uint4* __restrict__ tab, Fq12* __restrict__ f_out, uint8_t* __restrict__ ok_out, size_t n) {
+    size_t i = gtid();
+    bool live = i < n;
+    size_t j = live ? i : n - 1;
+    bool good = live && ok_in[j] != 0;
+    AffG1 pa = pa_in[j];
+    Fq12 f0 = fq12_one(), f1;
+    bool in0 = true;
+    const sp base = s_base();
+    int idx = 0;
+#define BN_LINE_STEP() do { const uint4* c = tab + (size_t)idx * 12 * n + j; idx++; \
+        if (in0) s_line_mul(f1, f0, c, n, pa, base); else s_line_mul(f0, f1, c, n, pa, base); in0 = !in0; } while (0)
+#pragma unroll 1
+    for (int k = 0; k < 64; k++) {
+        if (k) {
+            __syncthreads();
+            if (in0) s_fq12_sqr_na(f1, f0, base); else s_fq12_sqr_na(f0, f1, base);
+            in0 = !in0;
+            __syncthreads();
+        }
+        BN_LINE_STEP();
+        if (naf_digit(k)) BN_LINE_STEP();
+    }
+    BN_LINE_STEP();
+    BN_LINE_STEP();
+#undef BN_LINE_STEP
+    if (!live) return;
+    if (!good) f0 = fq12_one(); else if (!in0) f0 = f1;
+    f_out[i] = f0;
+    if (ok_out) ok_out[i] = good ? 1 : 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // product checks: one thread per check, shared squaring chain (groups::miller_loop_batch,
 // src/groups/mod.rs:609-640), line coefficients of the variable G2 points produced on the fly,

@@ -200,23 +200,30 @@ __device__ __noinline__ void s_f6_out(Fq2& out, sp Q, sp Va, sp Vb, sp Vc, int k
     }
     fq2_st(out, t);
 }
-// out = a + b, a - b (neg), a + xi b, a - xi b; local memory to local memory (Fq6/Fq12-level Karatsuba sums)
-__device__ __noinline__ void l_lin(Fq2& out, const Fq2& a, const Fq2& b, bool neg, bool xi) {
-    Fq2 x = fq2_ld(a), y = fq2_ld(b);
-    if (xi) {
+// out = a + b (mode 0), a - b (1), a + xi b (2), a - xi b (3), xi b (6); local memory to local memory (the Fq6/Fq12-level
+// Karatsuba sums around the slot products)
+#define BN_LIN_ADD 0
+#define BN_LIN_SUB 1
+#define BN_LIN_XI 2
+#define BN_LIN_ZERO_A 4
+__device__ __noinline__ void l_lin(Fq2& out, const Fq2& a, const Fq2& b, int mode) {
+    Fq2 x, y = fq2_ld(b);
+    if (mode & BN_LIN_ZERO_A) x = fq2_zero(); else x = fq2_ld(a);
+    if (mode & BN_LIN_XI) {
         Fq2 n;
         fq_lin9<true>(n.c0, y.c0, y.c1);
         fq_lin9<false>(n.c1, y.c1, y.c0);
         y = n;
     }
-    if (neg) { fq_sub(x.c0, x.c0, y.c0); fq_sub(x.c1, x.c1, y.c1); }
+    if (mode & BN_LIN_SUB) { fq_sub(x.c0, x.c0, y.c0); fq_sub(x.c1, x.c1, y.c1); }
     else { fq_add(x.c0, x.c0, y.c0); fq_add(x.c1, x.c1, y.c1); }
     fq2_st(out, x);
 }
-// out = a * b, operands and result in local memory, out not overlapping them.  post != 0 finishes an Fq12 Karatsuba product
-// in the same pass: out_i = (a b)_i - (aa_i + bb_i) for post = 1, (a b)_i - (aa_i - bb_i) for post = 2.
+// out = a * b, operands and result in local memory, out not overlapping them.  post != 0 finishes an Fq12-level Karatsuba
+// product in the same pass: out_i = (a b)_i - (p_i + r_i) for post = 1, (a b)_i - (p_i - r_i) for post = 2.
 // Karatsuba (6 products) in three stages of 3 + 2 + 1 products on the 7 slots; 15 calls.
-__device__ __noinline__ void s_fq6_mul(Fq6& out, const Fq6& a, const Fq6& b, const Fq6& aa, const Fq6& bb, int post, sp base) {
+__device__ __noinline__ void s_fq6_mul_p(Fq6& out, const Fq6& a, const Fq6& b, const Fq2& p0, const Fq2& r0, const Fq2& p1, const Fq2& r1,
+                                         const Fq2& p2, const Fq2& r2, int post, sp base) {
     const sp s0 = base, s1 = base + 64, s2 = base + 128, s3 = base + 192, s4 = base + 256, s5 = base + 320, s6 = base + 384;
     s_prep1(a.c0, a.c1, s0, s2, s4);
     s_prep1(b.c0, b.c1, s1, s3, s5);
@@ -230,23 +237,110 @@ __device__ __noinline__ void s_fq6_mul(Fq6& out, const Fq6& a, const Fq6& b, con
     s_prep1(a.c0, a.c2, BN_SKIP, BN_SKIP, s3);
     s_prep1(b.c0, b.c2, BN_SKIP, BN_SKIP, s6);
     s_mul(s3, s3, s6);                       // (a0 + a2)(b0 + b2)
-    s_f6_out(out.c0, s5, s2, s1, s0, 0, aa.c0, bb.c0, post);    // v0 + xi ((a1+a2)(b1+b2) - v1 - v2)
-    s_f6_out(out.c1, s4, s0, s2, s1, 1, aa.c1, bb.c1, post);    // (a0+a1)(b0+b1) - v0 - v1 + xi v2
-    s_f6_out(out.c2, s3, s0, s1, s2, 2, aa.c2, bb.c2, post);    // (a0+a2)(b0+b2) - v0 - v2 + v1
+    s_f6_out(out.c0, s5, s2, s1, s0, 0, p0, r0, post);    // v0 + xi ((a1+a2)(b1+b2) - v1 - v2)
+    s_f6_out(out.c1, s4, s0, s2, s1, 1, p1, r1, post);    // (a0+a1)(b0+b1) - v0 - v1 + xi v2
+    s_f6_out(out.c2, s3, s0, s1, s2, 2, p2, r2, post);    // (a0+a2)(b0+b2) - v0 - v2 + v1
+}
+__device__ __forceinline__ void s_fq6_mul(Fq6& out, const Fq6& a, const Fq6& b, const Fq6& aa, const Fq6& bb, int post, sp base) {
+    s_fq6_mul_p(out, a, b, aa.c0, bb.c0, aa.c1, bb.c1, aa.c2, bb.c2, post, base);
 }
 // r = a * b (conj_b: a * conj(b)); value of src/fields/fq12.rs:316-328.  r must not overlap a or b.
 __device__ __noinline__ void s_fq12_mul_na(Fq12& r, const Fq12& a, const Fq12& b, bool conj_b, sp base) {
     Fq6 aa, bb, sb;
+    const int m = conj_b ? BN_LIN_SUB : BN_LIN_ADD;
     s_fq6_mul(aa, a.c0, b.c0, aa, aa, 0, base);
     s_fq6_mul(bb, a.c1, b.c1, bb, bb, 0, base);
     // r.c0 doubles as the buffer of a0 + a1; c1 = (a0 + a1)(b0 +- b1) - (aa +- bb)
-    l_lin(r.c0.c0, a.c0.c0, a.c1.c0, false, false); l_lin(r.c0.c1, a.c0.c1, a.c1.c1, false, false); l_lin(r.c0.c2, a.c0.c2, a.c1.c2, false, false);
-    l_lin(sb.c0, b.c0.c0, b.c1.c0, conj_b, false); l_lin(sb.c1, b.c0.c1, b.c1.c1, conj_b, false); l_lin(sb.c2, b.c0.c2, b.c1.c2, conj_b, false);
+    l_lin(r.c0.c0, a.c0.c0, a.c1.c0, BN_LIN_ADD); l_lin(r.c0.c1, a.c0.c1, a.c1.c1, BN_LIN_ADD); l_lin(r.c0.c2, a.c0.c2, a.c1.c2, BN_LIN_ADD);
+    l_lin(sb.c0, b.c0.c0, b.c1.c0, m); l_lin(sb.c1, b.c0.c1, b.c1.c1, m); l_lin(sb.c2, b.c0.c2, b.c1.c2, m);
     s_fq6_mul(r.c1, r.c0, sb, aa, bb, conj_b ? 2 : 1, base);
     // c0 = aa +- v bb, v (b0, b1, b2) = (xi b2, b0, b1)
-    l_lin(r.c0.c0, aa.c0, bb.c2, conj_b, true);
-    l_lin(r.c0.c1, aa.c1, bb.c0, conj_b, false);
-    l_lin(r.c0.c2, aa.c2, bb.c1, conj_b, false);
+    l_lin(r.c0.c0, aa.c0, bb.c2, m | BN_LIN_XI);
+    l_lin(r.c0.c1, aa.c1, bb.c0, m);
+    l_lin(r.c0.c2, aa.c2, bb.c1, m);
+}
+// r = a^2, complex method (value of src/fields/fq12.rs:295-303): ab = a0 a1, c0 = (a0 + a1)(a0 + v a1) - ab - v ab, c1 = 2 ab.
+// r must not overlap a.
+__device__ __noinline__ void s_fq12_sqr_na(Fq12& r, const Fq12& a, sp base) {
+    Fq6 ab, sv;
+    Fq2 xab2;
+    s_fq6_mul(ab, a.c0, a.c1, ab, ab, 0, base);
+    // r.c1 doubles as the buffer of a0 + a1
+    l_lin(r.c1.c0, a.c0.c0, a.c1.c0, BN_LIN_ADD); l_lin(r.c1.c1, a.c0.c1, a.c1.c1, BN_LIN_ADD); l_lin(r.c1.c2, a.c0.c2, a.c1.c2, BN_LIN_ADD);
+    l_lin(sv.c0, a.c0.c0, a.c1.c2, BN_LIN_XI); l_lin(sv.c1, a.c0.c1, a.c1.c0, BN_LIN_ADD); l_lin(sv.c2, a.c0.c2, a.c1.c1, BN_LIN_ADD);
+    l_lin(xab2, ab.c2, ab.c2, BN_LIN_XI | BN_LIN_ZERO_A);
+    s_fq6_mul_p(r.c0, r.c1, sv, ab.c0, xab2, ab.c1, ab.c0, ab.c2, ab.c1, 1, base);
+    l_lin(r.c1.c0, ab.c0, ab.c0, BN_LIN_ADD); l_lin(r.c1.c1, ab.c1, ab.c1, BN_LIN_ADD); l_lin(r.c1.c2, ab.c2, ab.c2, BN_LIN_ADD);
+}
+
+// ---- line multiplication as six 3-term dot products (value of src/fields/fq12.rs:130-196) ----------------------
+// out = sum_{k<3} z[zi_k] * x[xi_k] with one Montgomery reduction per component: the three Fq2 products are accumulated
+// unreduced (each Karatsuba: z0 x0, z1 x1, (z0 + z1)(x0 + x1); sums < 12 q^2 < 2^512), then
+// c0 = sum z0 x0 - sum z1 x1 (+ q 2^256 when negative), c1 = sum (z0+z1)(x0+x1) - sum z0 x0 - sum z1 x1 < 6 q^2 (one
+// conditional subtraction of q 2^256 brings it below q 2^256).  z from the Fq12 in local memory (3-bit indices packed in
+// zi), x from the slots xbase + 64 * index (packed in xi).  Same IMAD work as the 13-product Karatsuba form, no additive glue.
+__device__ __noinline__ void s_dot3(Fq2& out, const Fq12& f, uint32_t zi, sp xbase, uint32_t xi) {
+    FqWide t0, t1, s;
+#pragma unroll
+    for (int i = 0; i < 16; i++) { t0.v[i] = 0; t1.v[i] = 0; s.v[i] = 0; }
+#pragma unroll 1
+    for (int k = 0; k < 3; k++) {
+        Fq2 z = fq2_ld(f12c(f, (zi >> (3 * k)) & 7));
+        Fq2 x = s_ld(xbase + 64 * ((xi >> (3 * k)) & 7));
+        FqWide p;
+        fq_mulwide(p, z.c0, x.c0); wide_add(t0, p);
+        fq_mulwide(p, z.c1, x.c1); wide_add(t1, p);
+        Fq sa, sb;
+        fq_add_noreduce(sa, z.c0, z.c1);
+        fq_add_noreduce(sb, x.c0, x.c1);
+        fq_mulwide(p, sa, sb); wide_add(s, p);
+    }
+    wide_sub(s, t0);                 // never borrows
+    wide_sub(s, t1);
+    wide_sub(t0, t1);                // + q 2^256 on borrow: in [0, q 2^256)
+    Fq hi, zero = fq_zero();
+#pragma unroll
+    for (int i = 0; i < 8; i++) hi.v[i] = s.v[8 + i];
+    fq_add(hi, hi, zero);            // high half < 1.14 q: one conditional subtraction of q
+#pragma unroll
+    for (int i = 0; i < 8; i++) s.v[8 + i] = hi.v[i];
+    Fq2 r;
+    fq_redc(r.c0, t0);
+    fq_redc(r.c1, s);
+    fq2_st(out, r);
+}
+// slots d <- c * k, dxi <- xi c k for the Fq2 coefficient c read from the line table (four 16-byte words, stride words apart):
+// ell_vv.scale(P.x) / ell_vw.scale(P.y) of src/groups/mod.rs:589
+__device__ __noinline__ void s_scale_xi(sp d, sp dxi, const uint4* __restrict__ g, size_t stride, const Fq& k) {
+    uint4 w0 = __ldg(g), w1 = __ldg(g + stride), w2 = __ldg(g + 2 * stride), w3 = __ldg(g + 3 * stride);
+    Fq kk = fq_ld(k);
+    Fq2 c, r, n;
+    c.c0.v[0] = w0.x; c.c0.v[1] = w0.y; c.c0.v[2] = w0.z; c.c0.v[3] = w0.w; c.c0.v[4] = w1.x; c.c0.v[5] = w1.y; c.c0.v[6] = w1.z; c.c0.v[7] = w1.w;
+    c.c1.v[0] = w2.x; c.c1.v[1] = w2.y; c.c1.v[2] = w2.z; c.c1.v[3] = w2.w; c.c1.v[4] = w3.x; c.c1.v[5] = w3.y; c.c1.v[6] = w3.z; c.c1.v[7] = w3.w;
+    fq_mul(r.c0, c.c0, kk);
+    fq_mul(r.c1, c.c1, kk);
+    s_st(d, r);
+    fq_lin9<true>(n.c0, r.c0, r.c1);
+    fq_lin9<false>(n.c1, r.c1, r.c0);
+    s_st(dxi, n);
+}
+// r = f * (ell_0 + ell_vv P.x v^2... ) i.e. one line evaluated at P and multiplied into f (line_mul of bn_curve.cuh).
+// With f = z0 + z3 w + z1 w^2 + z4 w^3 + z2 w^4 + z5 w^5 (w^6 = xi) and the line x0 + x4 w^3 + x2 w^4:
+//   z0' = z0 x0 + xi (z1 x2 + z4 x4)      z3' = z3 x0 + xi (z2 x4 + z4 x2)
+//   z1' = z1 x0 + xi (z5 x4 + z2 x2)      z4' = z4 x0 + z0 x4 + xi z5 x2
+//   z2' = z2 x0 + z0 x2 + z3 x4           z5' = z5 x0 + z3 x2 + z1 x4
+// Slots: 0 = x0, 1 = x2, 2 = x4, 3 = xi x2, 4 = xi x4.  r must not overlap f.
+#define BN_PK3(a, b, c) ((uint32_t)(a) | ((uint32_t)(b) << 3) | ((uint32_t)(c) << 6))
+__device__ __noinline__ void s_line_mul(Fq12& r, const Fq12& f, const uint4* __restrict__ c, size_t nt, const AffG1& p, sp base) {
+    sts128(base, __ldg(c)); sts128(base + 16, __ldg(c + nt)); sts128(base + 32, __ldg(c + 2 * nt)); sts128(base + 48, __ldg(c + 3 * nt));
+    s_scale_xi(base + 64, base + 192, c + 8 * nt, nt, p.x);      // x2 = ell_vv P.x
+    s_scale_xi(base + 128, base + 256, c + 4 * nt, nt, p.y);     // x4 = ell_vw P.y
+    s_dot3(r.c0.c0, f, BN_PK3(0, 1, 4), base, BN_PK3(0, 3, 4));
+    s_dot3(r.c0.c1, f, BN_PK3(1, 5, 2), base, BN_PK3(0, 4, 3));
+    s_dot3(r.c0.c2, f, BN_PK3(2, 0, 3), base, BN_PK3(0, 1, 2));
+    s_dot3(r.c1.c0, f, BN_PK3(3, 2, 4), base, BN_PK3(0, 4, 3));
+    s_dot3(r.c1.c1, f, BN_PK3(4, 0, 5), base, BN_PK3(0, 2, 3));
+    s_dot3(r.c1.c2, f, BN_PK3(5, 3, 1), base, BN_PK3(0, 1, 2));
 }
 
 // conj(a^u): same width-4 signed-window chain as fq12_exp_by_neg_z (bn_tower.cuh), on the slot bodies
