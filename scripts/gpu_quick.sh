@@ -6,5 +6,5 @@ timeout 600 python bench.py --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/
 tail -3 gpurun_out/pytest_gpu.log; python - <<'PY'
 import json
 d=json.loads(open('gpurun_out/bench_default.json').read().strip().splitlines()[-1])
-print(d['value'], d['e2e']['value'], d['roofline'].get('kernels_ms'), d['roofline']['frac'])
+print(d['value'], d['e2e']['value'], d['roofline'].get('kernels_ms'), d['roofline']['frac'], d['roofline']['whole_step_frac'])
 PY
