@@ -404,3 +404,33 @@ def test_pairing_across_table_chunk_boundary(eng):
     same = key[order][1:] == key[order][:-1]
     a, b = order[1:][same][:2000], order[:-1][same][:2000]
     assert (out[a] == out[b]).all()
+
+
+@pytest.mark.parametrize("n", [1, 63, 449, 1000])
+def test_slot_file_and_local_memory_paths_agree(eng, n):
+    """The slot-file kernels (one 448-thread block per SM with phase barriers: k_miller_table_sync, k_final_exp_hard_sync),
+    the 64-thread slot-file hard part and the local-memory kernels produce the oracle's bytes at batch sizes below, at and
+    across the block size, including pairs with points at infinity and the raw Miller values."""
+    import paritytech_bn_b200 as bn
+    g1, g2 = util.points_cpu(util.scalars(n, stream=71), util.scalars(n, stream=72))
+    g1 = g1.reshape(n, G1).copy(); g2 = g2.reshape(n, G2).copy()
+    if n > 10:
+        g1[3] = util.G1_INF; g2[n - 1] = util.G2_INF
+    g1, g2 = g1.reshape(-1), g2.reshape(-1)
+    m = min(n, 96)
+    exp = c.pairing_many(g1[:m * G1], g2[:m * G2], 0)
+    exp_f, exp_ok = c.miller_loop_many(g2[:m * G2], g1[:m * G1])
+    ref = eng.pairing(g1, g2)
+    assert ref[:m * GT].tobytes() == exp.tobytes()
+    for env in ({"BN254_FEXP_SMEM": "0", "BN254_MILLER_SMEM": "0"}, {"BN254_FEXP_SMEM": "1"}, {"BN254_FEXP_SMEM": "2", "BN254_MILLER_SMEM": "1"}):
+        os.environ.update(env)
+        try:
+            e2 = bn.Engine(0)
+        finally:
+            for k in env:
+                del os.environ[k]
+        got = e2.pairing(g1, g2)
+        f, ok = e2.miller_loop_many(g2, g1)
+        e2.close()
+        assert got.tobytes() == ref.tobytes(), env
+        assert f[:m * GT].tobytes() == exp_f.tobytes() and (ok[:m] == exp_ok).all(), env
