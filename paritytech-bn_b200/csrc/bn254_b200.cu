@@ -134,6 +134,9 @@ int bn254_ctx_create(int device, bn254_ctx** out) {
     { const char* e = getenv("BN254_MILLER_SMEM"); c->miller_smem = e ? atoi(e) : 1; }
     if (c->miller_smem) {
         cudaError_t ea = cudaFuncSetAttribute(k_miller_table_sync, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_FEXP_BLOCK * BN_SLOT_STRIDE);
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(k_miller_product_sync<1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_FEXP_BLOCK * BN_SLOT_STRIDE);
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(k_miller_product_sync<4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_FEXP_BLOCK * BN_SLOT_STRIDE);
+        if (ea == cudaSuccess) ea = cudaFuncSetAttribute(k_miller_product_sync<8, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_FEXP_BLOCK * BN_SLOT_STRIDE);
         if (ea != cudaSuccess) { delete c; return fail(BN254_ERR_CUDA, "cudaFuncSetAttribute(k_miller_table_sync)", ea); }
     }
     if (c->fexp_smem == 1) {
@@ -475,7 +478,10 @@ static int miller_products_dev(bn254_ctx* ctx, const G1* d_g1v, const G2* d_g2v,
     }
     // split path: affine conversion and line tables of the variable pairs (slot layout of table_slot), then one
     // product kernel per chunk of checks reading per-check and shared tables
+    // checks per chunk: at least 2^16 for up to 4 pairs per check (one full wave of the 448-thread kernel on 148 SMs; 4.4 GB of
+    // line tables at v = 4), 2^15 above
     size_t chunk = MILLER_CHUNK / v;
+    if (ctx->miller_smem) { size_t want = v <= 4 ? ((size_t)1 << 16) : ((size_t)1 << 15); if (chunk < want) chunk = want; }
     if (chunk > n_checks) chunk = n_checks;
     size_t pairs = chunk * v;
     size_t tab_bytes = (size_t)BN254_N_COEFFS * 12 * pairs * sizeof(uint4);
@@ -492,7 +498,15 @@ static int miller_products_dev(bn254_ctx* ctx, const G1* d_g1v, const G2* d_g2v,
         LAUNCH(ctx, k_pairs_to_affine, np, d_g2v + lo * v, d_g1v + lo * v, qa, pa, ok, np);
         LAUNCH(ctx, k_g2_lines_affine, np, (const AffG2*)qa, (const uint8_t*)ok, tabv, np, v);
         const G1* gs = d_g1s ? d_g1s + lo * m : nullptr;
-        if (v <= 1 && m <= 4) {
+        if (ctx->miller_smem) {
+            unsigned g = (unsigned)((nc + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK);
+            size_t smem = (size_t)BN_FEXP_BLOCK * BN_SLOT_STRIDE;
+            if (v <= 1 && m <= 4) k_miller_product_sync<1, 4><<<g, BN_FEXP_BLOCK, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
+            else if (v <= 4 && m <= 4) k_miller_product_sync<4, 4><<<g, BN_FEXP_BLOCK, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
+            else k_miller_product_sync<8, 8><<<g, BN_FEXP_BLOCK, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
+            ctx->launches.fetch_add(1);
+            CU(cudaGetLastError());
+        } else if (v <= 1 && m <= 4) {
             LAUNCH(ctx, (k_miller_product_tables<1, 4>), nc, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
         } else if (v <= 4 && m <= 4) {
             LAUNCH(ctx, (k_miller_product_tables<4, 4>), nc, (const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);

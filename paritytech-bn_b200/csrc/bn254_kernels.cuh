@@ -376,6 +376,56 @@ BN_KERNEL k_miller_product_tables(const AffG1* __restrict__ pa, const uint8_t* _
     }
     f_out[i] = f;
 }
+// Same on the slot file (one phase-synchronised block per SM; see k_miller_table_sync below).  The barriers are uniform:
+// every thread squares before every doubling coefficient but the first (a check without valid pairs squares 1) and runs
+// its own number of line multiplications between the barriers.
+template <int MAXV, int MAXS>
+__global__ void __launch_bounds__(BN_FEXP_BLOCK, 1) k_miller_product_sync(const AffG1* __restrict__ pa, const uint8_t* __restrict__ ok,
+                                  const uint4* __restrict__ tabv, int v, const G1* __restrict__ g1s, const uint4* __restrict__ tabs, int m,
+                                  Fq12* __restrict__ f_out, size_t n_checks) {
+    size_t i = gtid();
+    bool live = i < n_checks;
+    AffG1 P[MAXV];
+    AffG1 PS[MAXS];
+    int jv[MAXV], js[MAXS];
+    int nv = 0, ns = 0;
+    if (live) {
+        for (int j = 0; j < v; j++)          // skip semantics of pairing_batch, src/groups/mod.rs:909-920
+            if (ok[i * v + j]) { P[nv] = pa[i * v + j]; jv[nv++] = j; }
+        for (int j = 0; j < m; j++) {
+            G1 pp = g1s[i * m + j];
+            if (jac_to_affine(PS[ns], pp)) js[ns++] = j;
+        }
+    }
+    Fq12 f0 = fq12_one(), f1;
+    bool in0 = true;
+    const sp base = s_base();
+    size_t nt = n_checks * (size_t)v;
+#pragma unroll 1
+    for (int idx = 0; idx < BN_N_COEFFS; idx++) {
+        if (idx > 0 && coeff_is_doubling(idx)) {
+            __syncthreads();
+            if (in0) s_fq12_sqr_na(f1, f0, base); else s_fq12_sqr_na(f0, f1, base);
+            in0 = !in0;
+            __syncthreads();
+        }
+#pragma unroll 1
+        for (int j = 0; j < nv; j++) {
+            const uint4* c = tabv + (size_t)idx * 12 * nt + ((size_t)jv[j] * n_checks + i);
+            if (in0) s_line_mul(f1, f0, c, nt, P[j], base); else s_line_mul(f0, f1, c, nt, P[j], base);
+            in0 = !in0;
+        }
+#pragma unroll 1
+        for (int j = 0; j < ns; j++) {
+            const uint4* c = tabs + (size_t)idx * 12 * m + js[j];
+            if (in0) s_line_mul(f1, f0, c, (size_t)m, PS[j], base); else s_line_mul(f0, f1, c, (size_t)m, PS[j], base);
+            in0 = !in0;
+        }
+    }
+    if (!live) return;
+    if (!in0) f0 = f1;
+    f_out[i] = f0;
+}
 __global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS_MTAB) k_miller_table_affine(const AffG1* __restrict__ pa_in, const uint8_t* __restrict__ ok_in, const uint4* __restrict__ tab,
                                 Fq12* __restrict__ f_out, uint8_t* __restrict__ ok_out, size_t n) {
     size_t i = gtid();
