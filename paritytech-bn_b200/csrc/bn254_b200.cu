@@ -43,6 +43,8 @@ struct bn254_ctx {
     void* ws_ovr;      // when set, ctx_workspace hands out this region instead of the arena (one region per half batch)
     size_t ws_ovr_bytes;
     int pipeline;      // 1 (default): bn254_pairing_many runs large batches as two half batches on two streams (BN254_PIPELINE=0 disables)
+    unsigned force_block;   // non-zero: block size of the phase-synchronised kernels regardless of the batch (pipelined halves)
+    int sms;           // multiprocessor count (block size of the phase-synchronised kernels: one block per SM)
     int miller_smem;   // 1 (default): Miller loop from the table on the slot file (k_miller_table_sync; BN254_MILLER_SMEM=0: local memory)
     int fexp_smem;     // hard part of the final exponentiation (BN254_FEXP_SMEM): 2 (default) = shared-memory slot file, one
                        // phase-synchronised block per SM (k_final_exp_hard_sync); 1 = slot file, 64-thread blocks; 0 = local memory
@@ -70,6 +72,9 @@ struct DevBuf {
 };
 #define TRY(x) do { int _r = (x); if (_r != 0) return _r; } while (0)
 
+// Block size of the one-block-per-SM kernels: the batch spread over all SMs in whole warps, at most BN_FEXP_BLOCK threads
+// (2^16 pairings on 148 SMs: 448 threads, 147 blocks; 2^15: 224 threads; small batches: one warp per block).
+static inline unsigned sync_block(const struct bn254_ctx* ctx, size_t n);
 static inline unsigned grid_for(size_t n) { return (unsigned)((n + BN_BLOCK - 1) / BN_BLOCK); }
 #define LAUNCH(ctx, kernel, n, ...)                                                        \
     do {                                                                                   \
@@ -80,6 +85,14 @@ static inline unsigned grid_for(size_t n) { return (unsigned)((n + BN_BLOCK - 1)
         }                                                                                  \
     } while (0)
 
+static inline unsigned sync_block(const bn254_ctx* ctx, size_t n) {
+    if (ctx->force_block) return ctx->force_block;
+    size_t per_sm = (n + (size_t)ctx->sms - 1) / (size_t)ctx->sms;
+    size_t b = ((per_sm + 31) / 32) * 32;
+    if (b < 32) b = 32;
+    if (b > BN_FEXP_BLOCK) b = BN_FEXP_BLOCK;
+    return (unsigned)b;
+}
 static int use(bn254_ctx* ctx) {
     if (!ctx) return fail(BN254_ERR_ARG, "null context");
     CU(cudaSetDevice(ctx->device));
@@ -126,6 +139,10 @@ int bn254_ctx_create(int device, bn254_ctx** out) {
     c->io_bytes = 0;
     c->ws_ovr = nullptr;
     c->ws_ovr_bytes = 0;
+    c->force_block = 0;
+    c->sms = 148;
+    cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, device);
+    if (c->sms <= 0) c->sms = 148;
     c->stream2 = nullptr;
     { const char* e = getenv("BN254_PIPELINE"); c->pipeline = !(e && e[0] == '0'); }
     { const char* e = getenv("BN254_FUSED_MILLER"); c->split_miller = (e && e[0] == '1') ? 0 : 1; }
@@ -212,8 +229,8 @@ static int final_exp_dev(bn254_ctx* ctx, const Fq12* d_in, Fq12* d_out, uint8_t*
     uint8_t* flags = (uint8_t*)ws + vals;
     LAUNCH(ctx, k_final_exp_easy, n, d_in, t, flags, n);
     if (ctx->fexp_smem == 2) {
-        unsigned g = (unsigned)((n + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK);
-        k_final_exp_hard_sync<<<g, BN_FEXP_BLOCK, BN_FEXP_BLOCK * BN_SLOT_STRIDE, ctx->stream>>>((const Fq12*)t, (const uint8_t*)flags, d_out, d_some, d_is_one, n);
+        unsigned bs = sync_block(ctx, n), g = (unsigned)((n + bs - 1) / bs);
+        k_final_exp_hard_sync<<<g, bs, bs * BN_SLOT_STRIDE, ctx->stream>>>((const Fq12*)t, (const uint8_t*)flags, d_out, d_some, d_is_one, n);
         ctx->launches.fetch_add(1);
         CU(cudaGetLastError());
         return 0;
@@ -244,8 +261,8 @@ static int ctx_io(bn254_ctx* ctx, const size_t* sizes, int count, void** out) {
 // Miller loop of m pairs from their line tables: slot-file kernel (one 448-thread block per SM) or the local-memory kernel
 static int miller_table_launch(bn254_ctx* ctx, const AffG1* pa, const uint8_t* ok, const uint4* tab, Fq12* f, uint8_t* ok_out, size_t m) {
     if (ctx->miller_smem) {
-        unsigned g = (unsigned)((m + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK);
-        k_miller_table_sync<<<g, BN_FEXP_BLOCK, BN_FEXP_BLOCK * BN_SLOT_STRIDE, ctx->stream>>>(pa, ok, tab, f, ok_out, m);
+        unsigned bs = sync_block(ctx, m), g = (unsigned)((m + bs - 1) / bs);
+        k_miller_table_sync<<<g, bs, bs * BN_SLOT_STRIDE, ctx->stream>>>(pa, ok, tab, f, ok_out, m);
         ctx->launches.fetch_add(1);
         CU(cudaGetLastError());
         return 0;
@@ -373,7 +390,7 @@ int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_
     TRY(ctx_io(ctx, sz, 3, d));
     // Pinned (mapped) output buffer: the final-exponentiation kernel stores its 384-byte results straight into host memory.
     char* mapped = ctx->zerocopy_out ? (char*)mapped_device_ptr(gt_out) : nullptr;
-    const size_t PIPE_MIN = (size_t)1 << 15;
+    const size_t PIPE_MIN = (size_t)1 << 16;   // below this the halves would leave SMs idle (74 blocks of 448 threads per half at 2^16)
     if (!ctx->pipeline || n < PIPE_MIN || !ctx->split_miller) {
         TRY(pairing_many_enqueue(ctx, (const char*)g1, (const char*)g2, (char*)gt_out, mapped, d, 0, n));
         CU(cudaStreamSynchronize(ctx->stream));
@@ -395,6 +412,7 @@ int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_
     CU(cudaEventRecord(ctx->ev_fork, main_stream));
     CU(cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
     ctx->ws_ovr = ws; ctx->ws_ovr_bytes = wA;
+    ctx->force_block = BN_FEXP_BLOCK;   // each half on its own SMs: two smaller blocks per SM would interleave their phases
     int rc = pairing_many_enqueue(ctx, (const char*)g1, (const char*)g2, (char*)gt_out, mapped, d, 0, nA);
     if (rc == 0) {
         ctx->stream = ctx->stream2;
@@ -403,6 +421,7 @@ int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_
         ctx->stream = main_stream;
     }
     ctx->ws_ovr = nullptr; ctx->ws_ovr_bytes = 0;
+    ctx->force_block = 0;
     cudaEventRecord(ctx->ev_join, ctx->stream2);
     cudaStreamWaitEvent(main_stream, ctx->ev_join, 0);
     cudaError_t es = cudaStreamSynchronize(main_stream);
@@ -499,11 +518,11 @@ static int miller_products_dev(bn254_ctx* ctx, const G1* d_g1v, const G2* d_g2v,
         LAUNCH(ctx, k_g2_lines_affine, np, (const AffG2*)qa, (const uint8_t*)ok, tabv, np, v);
         const G1* gs = d_g1s ? d_g1s + lo * m : nullptr;
         if (ctx->miller_smem) {
-            unsigned g = (unsigned)((nc + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK);
-            size_t smem = (size_t)BN_FEXP_BLOCK * BN_SLOT_STRIDE;
-            if (v <= 1 && m <= 4) k_miller_product_sync<1, 4><<<g, BN_FEXP_BLOCK, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
-            else if (v <= 4 && m <= 4) k_miller_product_sync<4, 4><<<g, BN_FEXP_BLOCK, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
-            else k_miller_product_sync<8, 8><<<g, BN_FEXP_BLOCK, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
+            unsigned bs = sync_block(ctx, nc), g = (unsigned)((nc + bs - 1) / bs);
+            size_t smem = (size_t)bs * BN_SLOT_STRIDE;
+            if (v <= 1 && m <= 4) k_miller_product_sync<1, 4><<<g, bs, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
+            else if (v <= 4 && m <= 4) k_miller_product_sync<4, 4><<<g, bs, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
+            else k_miller_product_sync<8, 8><<<g, bs, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
             ctx->launches.fetch_add(1);
             CU(cudaGetLastError());
         } else if (v <= 1 && m <= 4) {
