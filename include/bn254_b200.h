@@ -178,7 +178,9 @@ int bn254_pairing_product_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1
 /* ---- field-level test hooks (parity tests of the arithmetic kernels) ---------------------------- */
 /* op: 0 = Fq mul, 1 = Fq add, 2 = Fq sub, 3 = Fq2 mul, 4 = Fq2 sqr, 5 = Fq6 mul, 6 = Fq12 mul,
  *     7 = Fq12 sqr, 8 = Fq12 cyclotomic_squared, 9 = Fq inverse (b ignored),
- *     10 = Fq2 mul_by_nonresidue (xi = 9 + u, src/fields/fq2.rs:55-57; b ignored) */
+ *     10 = Fq2 mul_by_nonresidue (xi = 9 + u, src/fields/fq2.rs:55-57; b ignored);
+ *     the shared-memory slot-file bodies one call at a time: 11 = sum of three Fq2 products a[k] * b[k] (unit 192 B, result in
+ *     the first 64 B), 12 = Fq12 mul, 13 = Fq12 sqr, 14 = cyclotomic_squared, 15 = Fq6 mul */
 int bn254_field_op_many(bn254_ctx* ctx, int op, const void* a, const void* b, void* out, size_t n);
 
 /* ---- roofline microbenchmarks (register-only; report via bench.py) ------------------------------ */

@@ -22,7 +22,10 @@ ERR_TO_AFFINE = 1
 
 FIELD_OPS = {"fq_mul": (0, 32), "fq_add": (1, 32), "fq_sub": (2, 32), "fq2_mul": (3, 64), "fq2_sqr": (4, 64),
              "fq6_mul": (5, 192), "fq12_mul": (6, 384), "fq12_sqr": (7, 384), "fq12_cyclotomic_sqr": (8, 384),
-             "fq_inv": (9, 32), "fq2_mul_by_xi": (10, 64)}
+             "fq_inv": (9, 32), "fq2_mul_by_xi": (10, 64),
+             # the slot-file bodies of csrc/bn_slots.cuh, one call at a time
+             "slot_dot3": (11, 192), "slot_fq12_mul": (12, 384), "slot_fq12_sqr": (13, 384),
+             "slot_cyclotomic_sqr": (14, 384), "slot_fq6_mul": (15, 192)}
 
 
 class BnError(RuntimeError):

@@ -975,16 +975,22 @@ int bn254_pairing_product_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1
 int bn254_field_op_many(bn254_ctx* ctx, int op, const void* a, const void* b, void* out, size_t n) {
     TRY(use(ctx));
     if (n == 0) return 0;
-    static const size_t unit_of[11] = {32, 32, 32, 64, 64, 192, 384, 384, 384, 32, 64};
-    if (op < 0 || op > 10 || !a || !out) return fail(BN254_ERR_ARG, "bad argument");
-    bool binary = (op == 0 || op == 1 || op == 2 || op == 3 || op == 5 || op == 6);
+    static const size_t unit_of[16] = {32, 32, 32, 64, 64, 192, 384, 384, 384, 32, 64, 192, 384, 384, 384, 192};
+    if (op < 0 || op > 15 || !a || !out) return fail(BN254_ERR_ARG, "bad argument");
+    bool binary = (op == 0 || op == 1 || op == 2 || op == 3 || op == 5 || op == 6 || op == 11 || op == 12 || op == 15);
     if (binary && !b) return fail(BN254_ERR_ARG, "null pointer");
     size_t bytes = unit_of[op] * n;
     DevBuf x, y, o;
     TRY(x.alloc(bytes)); TRY(y.alloc(bytes)); TRY(o.alloc(bytes));
     TRY(h2d(ctx, x.p, a, bytes));
     if (binary) TRY(h2d(ctx, y.p, b, bytes));
-    LAUNCH(ctx, k_field_op, n, op, x.as<uint4>(), y.as<uint4>(), o.as<uint4>(), n);
+    if (op >= 11) {
+        k_slot_op<<<grid_for(n), BN_BLOCK, BN_BLOCK * BN_SLOT_STRIDE, ctx->stream>>>(op, x.as<uint4>(), y.as<uint4>(), o.as<uint4>(), n);
+        ctx->launches.fetch_add(1);
+        CU(cudaGetLastError());
+    } else {
+        LAUNCH(ctx, k_field_op, n, op, x.as<uint4>(), y.as<uint4>(), o.as<uint4>(), n);
+    }
     TRY(d2h(ctx, out, o.p, bytes));
     CU(cudaStreamSynchronize(ctx->stream));
     return 0;

@@ -602,6 +602,33 @@ BN_KERNEL k_field_op(int op, const uint4* __restrict__ a, const uint4* __restric
     }
 }
 
+// slot-file test hook (ops 11..15 of bn254_field_op_many): the bodies of bn_slots.cuh one call at a time, launched with
+// BN_BLOCK * BN_SLOT_STRIDE bytes of dynamic shared memory.  11: out[0] = sum_k a[k] * b[k] over three Fq2 pairs (s_dot3, unit
+// 192 B, the other two output coefficients zero); 12: Fq12 product; 13: Fq12 squaring; 14: cyclotomic squaring; 15: Fq6 product.
+BN_KERNEL k_slot_op(int op, const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ out, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    const sp base = s_base();
+    if (op == 11) {
+        Fq12 z = fq12_zero();
+        Fq6 x = reinterpret_cast<const Fq6*>(b)[i], r = fq6_zero();
+        z.c0 = reinterpret_cast<const Fq6*>(a)[i];
+        s_in(base, x.c0); s_in(base + 64, x.c1); s_in(base + 128, x.c2);
+        s_dot3(r.c0, z, BN_PK3(0, 1, 2), base, BN_PK3(0, 1, 2));
+        reinterpret_cast<Fq6*>(out)[i] = r;
+    } else if (op == 15) {
+        Fq6 x = reinterpret_cast<const Fq6*>(a)[i], y = reinterpret_cast<const Fq6*>(b)[i], r;
+        s_fq6_mul(r, x, y, x, x, 0, base);
+        reinterpret_cast<Fq6*>(out)[i] = r;
+    } else {
+        Fq12 x = reinterpret_cast<const Fq12*>(a)[i], r;
+        if (op == 12) { Fq12 y = reinterpret_cast<const Fq12*>(b)[i]; s_fq12_mul_na(r, x, y, false, base); }
+        else if (op == 13) s_fq12_sqr_na(r, x, base);
+        else s_cyclotomic_sqr_na(r, x, base);
+        reinterpret_cast<Fq12*>(out)[i] = r;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // roofline microbenchmarks: register-only chains.  kind 0: mad.lo.u32 (IMAD), 1: mad.wide.u32
 // (IMAD.WIDE), 2: dependent Fq Montgomery multiplications (2 independent streams per thread).

@@ -434,3 +434,54 @@ def test_slot_file_and_local_memory_paths_agree(eng, n):
         e2.close()
         assert got.tobytes() == ref.tobytes(), env
         assert f[:m * GT].tobytes() == exp_f.tobytes() and (ok[:m] == exp_ok).all(), env
+
+
+@pytest.mark.parametrize("name,unit,ref", [
+    ("slot_fq6_mul", 192, c.fq6_mul), ("slot_fq12_mul", 384, c.fq12_mul),
+])
+def test_slot_file_binary_ops(eng, name, unit, ref):
+    """The shared-memory slot-file bodies (csrc/bn_slots.cuh: fused Karatsuba stages) one call at a time against the oracle."""
+    rng = np.random.default_rng(11)
+    a, b = _rand_fq_elems(rng, unit // 32, 300), _rand_fq_elems(rng, unit // 32, 300)
+    assert eng.field_op(name, a, b).tobytes() == ref(a, b).tobytes()
+    assert eng.field_op(name, a, a).tobytes() == ref(a, a).tobytes()
+
+
+@pytest.mark.parametrize("name,ref", [("slot_fq12_sqr", c.fq12_sqr), ("slot_cyclotomic_sqr", c.fq12_cyclotomic_squared)])
+def test_slot_file_unary_ops(eng, name, ref):
+    rng = np.random.default_rng(12)
+    a = _rand_fq_elems(rng, 12, 300)
+    assert eng.field_op(name, a).tobytes() == ref(a).tobytes()
+
+
+def test_slot_dot3_bounds(eng):
+    """s_dot3 accumulates three Fq2 products unreduced (sums up to 12 q^2) and reduces once per component; its bound argument
+    (imaginary part < 1.14 q 2^256 before the conditional subtraction, real part brought into [0, q 2^256)) is exercised with
+    every coefficient at q - 1, 0, 1 and mixed extremes next to random inputs."""
+    rng = np.random.default_rng(13)
+    Q = o.Q
+    ext = [Q - 1, 0, 1, Q - 2, (Q - 1) // 2, (Q + 1) // 2]
+    rows_a, rows_b = [], []
+    for x in ext:
+        for y in ext:
+            rows_a.append([x] * 6); rows_b.append([y] * 6)                 # all coefficients equal extremes
+            rows_a.append([x, 0] * 3); rows_b.append([y, 0] * 3)           # real parts only
+            rows_a.append([0, x] * 3); rows_b.append([0, y] * 3)           # imaginary parts only: most negative real sum
+            rows_a.append([x, y] * 3); rows_b.append([y, x] * 3)
+    def enc(rows):
+        return np.frombuffer(b"".join(o.fq_to_mont(v).to_bytes(32, "little") for r in rows for v in r), dtype=np.uint8).copy()
+    a = np.concatenate([enc(rows_a), _rand_fq_elems(rng, 6, 2000)])
+    b = np.concatenate([enc(rows_b), _rand_fq_elems(rng, 6, 2000)])
+    n = len(a) // 192
+    got = eng.field_op("slot_dot3", a, b).reshape(n, 192)
+    A, B = a.reshape(n, 3, 64), b.reshape(n, 3, 64)
+    acc = None
+    for k in range(3):
+        p = c.fq2_mul(A[:, k].reshape(-1).copy(), B[:, k].reshape(-1).copy())
+        if acc is None:
+            acc = p
+        else:
+            acc = np.concatenate([c.fq_add(acc.reshape(n, 2, 32)[:, h].reshape(-1).copy(), p.reshape(n, 2, 32)[:, h].reshape(-1).copy()).reshape(n, 1, 32)
+                                  for h in range(2)], axis=1).reshape(-1)
+    assert got[:, :64].tobytes() == acc.tobytes()
+    assert not got[:, 64:].any()
