@@ -290,7 +290,8 @@ def main():
     fexp_mode = os.environ.get("BN254_FEXP_SMEM", "2")
     fexp_name = {"2": "k_final_exp_easy+k_final_exp_hard_sync", "1": "k_final_exp_easy+k_final_exp_hard_s"}.get(fexp_mode, "k_final_exp_many")
     mtab_name = "k_miller_table_affine" if os.environ.get("BN254_MILLER_SMEM", "1") == "0" else "k_miller_table_sync"
-    cands = [(fexp_name, t_fexp, FQMUL_FINALEXP), (mtab_name, t_mtab, 6045), ("k_g2_lines_affine", t_lines, 2916)]
+    lines_name = "k_g2_lines_affine" if os.environ.get("BN254_LINES_SMEM", "1") == "0" else "k_g2_lines_sync"
+    cands = [(fexp_name, t_fexp, FQMUL_FINALEXP), (mtab_name, t_mtab, 6045), (lines_name, t_lines, 2916)]
     if t_lines == 0.0:
         cands = [(fexp_name, t_fexp, FQMUL_FINALEXP), ("k_miller_many", t_mtab, FQMUL_MILLER)]
     dom_name, dom_ms, dom_fq = max(cands, key=lambda c: c[1])
@@ -323,9 +324,9 @@ def main():
                      "peak_theoretical": sms * 64 * sm_mhz * 1e6 / 1e12 if sm_mhz else None,
                      "algorithmic_imad_eq_per_pairing": FQMUL_PAIRING * FQMUL_IMAD_EQ,
                      "whole_step_frac": FQMUL_PAIRING * FQMUL_IMAD_EQ * n * world * args.steps / (total_ms * 1e-3) / (peak_measured * world),
-                     "kernels_ms": {"k_pairs_to_affine": t_aff, "k_g2_lines_affine": t_lines, mtab_name: t_mtab, fexp_name: t_fexp,
+                     "kernels_ms": {"k_pairs_to_affine": t_aff, lines_name: t_lines, mtab_name: t_mtab, fexp_name: t_fexp,
                                     "miller_total": t_miller},
-                     "g2precomp_stream_hbm_gbs": {"write_k_g2_lines_affine": table_bytes / (t_lines * 1e-3) / 1e9 if t_lines else None,
+                     "g2precomp_stream_hbm_gbs": {"write_" + lines_name: table_bytes / (t_lines * 1e-3) / 1e9 if t_lines else None,
                                                   "read_" + mtab_name: table_bytes / (t_mtab * 1e-3) / 1e9 if t_mtab else None,
                                                   "bytes": table_bytes, "hbm_peak_gbs": HBM_PEAK_GBS},
                      "microbench_ops_per_s": micro},

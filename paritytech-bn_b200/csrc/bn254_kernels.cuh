@@ -5,6 +5,7 @@
 #include "bn_curve.cuh"
 #include "bn_wire.cuh"
 #include "bn_slots.cuh"
+#include "bn_slots_curve.cuh"
 
 namespace bn {
 
@@ -344,6 +345,42 @@ __global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS_LINES) k_g2_lines_affi
     TableSink s;
     s.tab = tab; s.n_tables = n; s.j = table_slot(i, v, n); s.idx = 0;
     g2_walk_lines(q, s);
+}
+// Same walk on the slot file (bn_slots_curve.cuh), one phase-synchronised block per SM: doubling steps and addition steps
+// alternate under block barriers (the NAF digits are constants, so every thread takes the same steps).  Threads without a
+// valid point walk a dummy point and store nothing.
+__global__ void __launch_bounds__(BN_FEXP_BLOCK, 1) k_g2_lines_sync(const AffG2* __restrict__ qa, const uint8_t* __restrict__ ok,
+                                                                     uint4* __restrict__ tab, size_t n, size_t v) {
+    size_t i = gtid();
+    bool live = i < n && ok[i] != 0;
+    AffG2 q, qn, q1, q2;
+    if (live) q = qa[i]; else { q.x = fq2_one(); q.y = fq2_one(); }
+    qn.x = q.x; fq2_neg(qn.y, q.y);
+    g2_mul_by_q(q1, q);
+    g2_mul_by_q(q2, q1);
+    fq2_neg(q2.y, q2.y);
+    const sp base = s_base();
+    s_in(base, q.x); s_in(base + 64, q.y);
+    { Fq2 one = fq2_one(); s_st(base + 128, one); }
+    LineOut o;
+    o.tab = tab + (live ? table_slot(i, v, n) : 0);
+    o.stride = n;
+    o.live = live;
+    int idx = 0;
+#pragma unroll 1
+    for (int k = 0; k < 64; k++) {
+        __syncthreads();
+        s_g2_doubling_step(base, o, idx++);
+        uint32_t d = naf_digit(k);
+        if (d != 0) {
+            __syncthreads();
+            if (d == 1) s_g2_mixed_addition_step(base, q.x, q.y, o, idx++);
+            else s_g2_mixed_addition_step(base, q.x, qn.y, o, idx++);
+        }
+    }
+    __syncthreads();
+    s_g2_mixed_addition_step(base, q1.x, q1.y, o, idx++);
+    s_g2_mixed_addition_step(base, q2.x, q2.y, o, idx++);
 }
 // Product checks from line tables: one thread per check, shared squaring chain (groups::miller_loop_batch,
 // src/groups/mod.rs:609-640).  Variable pairs: affine P / ok flags / per-pair tables from the two kernels above

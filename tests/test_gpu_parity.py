@@ -422,7 +422,7 @@ def test_slot_file_and_local_memory_paths_agree(eng, n):
     exp_f, exp_ok = c.miller_loop_many(g2[:m * G2], g1[:m * G1])
     ref = eng.pairing(g1, g2)
     assert ref[:m * GT].tobytes() == exp.tobytes()
-    for env in ({"BN254_FEXP_SMEM": "0", "BN254_MILLER_SMEM": "0"}, {"BN254_FEXP_SMEM": "1"}, {"BN254_FEXP_SMEM": "2", "BN254_MILLER_SMEM": "1"}):
+    for env in ({"BN254_FEXP_SMEM": "0", "BN254_MILLER_SMEM": "0", "BN254_LINES_SMEM": "0"}, {"BN254_FEXP_SMEM": "1"}, {"BN254_FEXP_SMEM": "2", "BN254_MILLER_SMEM": "1"}):
         os.environ.update(env)
         try:
             e2 = bn.Engine(0)
