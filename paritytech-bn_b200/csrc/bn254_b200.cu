@@ -43,6 +43,7 @@ struct bn254_ctx {
     void* ws_ovr;      // when set, ctx_workspace hands out this region instead of the arena (one region per half batch)
     size_t ws_ovr_bytes;
     int pipeline;      // 1 (default): bn254_pairing_many runs large batches as two half batches on two streams (BN254_PIPELINE=0 disables)
+    int big_blocks;    // 1 (default): 512-thread blocks for batches of more than one wave (BN254_BIG_BLOCKS=0: always at most 448)
     unsigned force_block;   // non-zero: block size of the phase-synchronised kernels regardless of the batch (pipelined halves)
     int sms;           // multiprocessor count (block size of the phase-synchronised kernels: one block per SM)
     int lines_smem;    // 1 (default): G2 line tables on the slot file (k_g2_lines_sync; BN254_LINES_SMEM=0: local-memory kernel)
@@ -88,12 +89,25 @@ static inline unsigned grid_for(size_t n) { return (unsigned)((n + BN_BLOCK - 1)
 
 static inline unsigned sync_block(const bn254_ctx* ctx, size_t n) {
     if (ctx->force_block) return ctx->force_block;
+    // more than one wave of 448-thread blocks: 512-thread blocks on 6 slots per thread -- four warps on every sub-partition
+    // instead of 4 + 4 + 3 + 3 (DESIGN F14)
+    // -- when that saves waves: a 512-thread wave takes 1.10 x a 448-thread one (measured at 2^19: 23.5 against 21.4 ms for
+    // the whole path), so 2^19 (7 against 8 waves) and 2^20 (14 against 16) gain 4 %, 2^17 and 2^18 (same wave count) would lose
+    if (ctx->big_blocks == 2 && n > BN_SYNC_MAX_BLOCK) return BN_SYNC_MAX_BLOCK;
+    if (ctx->big_blocks && n > (size_t)ctx->sms * BN_FEXP_BLOCK) {
+        size_t sm = (size_t)ctx->sms;
+        size_t w7 = ((n + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK + sm - 1) / sm;
+        size_t w6 = ((n + BN_SYNC_MAX_BLOCK - 1) / BN_SYNC_MAX_BLOCK + sm - 1) / sm;
+        if (w6 * 11 < w7 * 10) return BN_SYNC_MAX_BLOCK;
+        return BN_FEXP_BLOCK;
+    }
     size_t per_sm = (n + (size_t)ctx->sms - 1) / (size_t)ctx->sms;
     size_t b = ((per_sm + 31) / 32) * 32;
     if (b < 32) b = 32;
     if (b > BN_FEXP_BLOCK) b = BN_FEXP_BLOCK;
     return (unsigned)b;
 }
+static inline size_t sync_smem(unsigned bs) { return (size_t)bs * (bs > BN_SLOT_BLOCK7 ? BN_SLOT_STRIDE6 : BN_SLOT_STRIDE); }
 static int use(bn254_ctx* ctx) {
     if (!ctx) return fail(BN254_ERR_ARG, "null context");
     CU(cudaSetDevice(ctx->device));
@@ -141,6 +155,7 @@ int bn254_ctx_create(int device, bn254_ctx** out) {
     c->ws_ovr = nullptr;
     c->ws_ovr_bytes = 0;
     c->force_block = 0;
+    { const char* e = getenv("BN254_BIG_BLOCKS"); c->big_blocks = e ? atoi(e) : 1; }   // 2: 512-thread blocks for every batch above 512 (tests)
     c->sms = 148;
     cudaDeviceGetAttribute(&c->sms, cudaDevAttrMultiProcessorCount, device);
     if (c->sms <= 0) c->sms = 148;
@@ -236,7 +251,7 @@ static int final_exp_dev(bn254_ctx* ctx, const Fq12* d_in, Fq12* d_out, uint8_t*
     LAUNCH(ctx, k_final_exp_easy, n, d_in, t, flags, n);
     if (ctx->fexp_smem == 2) {
         unsigned bs = sync_block(ctx, n), g = (unsigned)((n + bs - 1) / bs);
-        k_final_exp_hard_sync<<<g, bs, bs * BN_SLOT_STRIDE, ctx->stream>>>((const Fq12*)t, (const uint8_t*)flags, d_out, d_some, d_is_one, n);
+        k_final_exp_hard_sync<<<g, bs, sync_smem(bs), ctx->stream>>>((const Fq12*)t, (const uint8_t*)flags, d_out, d_some, d_is_one, n);
         ctx->launches.fetch_add(1);
         CU(cudaGetLastError());
         return 0;
@@ -269,8 +284,10 @@ static int lines_launch(bn254_ctx* ctx, const AffG2* qa, const uint8_t* ok, uint
     // one wave only: with more work the 64-thread kernel reaches 16 warps per SM (the slot file allows 14) and is faster
     // (2^17 points: 5.6 against 6.0 ms; 2^16: 3.24 against 3.01 ms)
     if (ctx->lines_smem && m <= (size_t)ctx->sms * BN_FEXP_BLOCK) {
-        unsigned bs = sync_block(ctx, m), g = (unsigned)((m + bs - 1) / bs);
-        k_g2_lines_sync<<<g, bs, bs * BN_SLOT_STRIDE, ctx->stream>>>(qa, ok, tab, m, v);
+        unsigned bs = sync_block(ctx, m);
+        if (bs > BN_FEXP_BLOCK) bs = BN_FEXP_BLOCK;   // this kernel uses all 7 slots
+        unsigned g = (unsigned)((m + bs - 1) / bs);
+        k_g2_lines_sync<<<g, bs, sync_smem(bs), ctx->stream>>>(qa, ok, tab, m, v);
         ctx->launches.fetch_add(1);
         CU(cudaGetLastError());
         return 0;
@@ -282,7 +299,7 @@ static int lines_launch(bn254_ctx* ctx, const AffG2* qa, const uint8_t* ok, uint
 static int miller_table_launch(bn254_ctx* ctx, const AffG1* pa, const uint8_t* ok, const uint4* tab, Fq12* f, uint8_t* ok_out, size_t m) {
     if (ctx->miller_smem) {
         unsigned bs = sync_block(ctx, m), g = (unsigned)((m + bs - 1) / bs);
-        k_miller_table_sync<<<g, bs, bs * BN_SLOT_STRIDE, ctx->stream>>>(pa, ok, tab, f, ok_out, m);
+        k_miller_table_sync<<<g, bs, sync_smem(bs), ctx->stream>>>(pa, ok, tab, f, ok_out, m);
         ctx->launches.fetch_add(1);
         CU(cudaGetLastError());
         return 0;
@@ -539,7 +556,7 @@ static int miller_products_dev(bn254_ctx* ctx, const G1* d_g1v, const G2* d_g2v,
         const G1* gs = d_g1s ? d_g1s + lo * m : nullptr;
         if (ctx->miller_smem) {
             unsigned bs = sync_block(ctx, nc), g = (unsigned)((nc + bs - 1) / bs);
-            size_t smem = (size_t)bs * BN_SLOT_STRIDE;
+            size_t smem = sync_smem(bs);
             if (v <= 1 && m <= 4) k_miller_product_sync<1, 4><<<g, bs, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
             else if (v <= 4 && m <= 4) k_miller_product_sync<4, 4><<<g, bs, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);
             else k_miller_product_sync<8, 8><<<g, bs, smem, ctx->stream>>>((const AffG1*)pa, (const uint8_t*)ok, (const uint4*)tabv, (int)v, gs, tab, (int)m, d_f + lo, nc);

@@ -139,9 +139,10 @@ __global__ void __launch_bounds__(BN_BLOCK, 7) k_final_exp_hard_s(const Fq12* __
 // same, one block of BN_FEXP_BLOCK threads per SM with phase barriers (bn_slots.cuh, s_phase): threads past n run the
 // schedule on zeros so that every barrier is reached by the whole block
 #ifndef BN_FEXP_BLOCK
-#define BN_FEXP_BLOCK 448
+#define BN_FEXP_BLOCK 448               /* one-wave block: 7 slots per thread */
 #endif
-__global__ void __launch_bounds__(BN_FEXP_BLOCK, 1) k_final_exp_hard_sync(const Fq12* __restrict__ in, const uint8_t* __restrict__ some_in,
+#define BN_SYNC_MAX_BLOCK 512           /* batches of more than one wave: 16 warps per SM on 6 slots per thread */
+__global__ void __launch_bounds__(BN_SYNC_MAX_BLOCK, 1) k_final_exp_hard_sync(const Fq12* __restrict__ in, const uint8_t* __restrict__ some_in,
                            Fq12* __restrict__ out, uint8_t* __restrict__ some, uint8_t* __restrict__ is_one, size_t n) {
     size_t i = gtid();
     bool live = i < n;
@@ -161,7 +162,7 @@ __global__ void __launch_bounds__(BN_FEXP_BLOCK, 1) k_final_exp_hard_sync(const 
 // Miller loop from the line table on the slot file, one phase-synchronised block per SM: the squaring code and the
 // line-multiplication code alternate under block barriers so that each fits the instruction cache on its own
 // (G2Precomp::miller_loop, src/groups/mod.rs:580-606; same values as k_miller_table_affine).
-__global__ void __launch_bounds__(BN_FEXP_BLOCK, 1) k_miller_table_sync(const AffG1* __restrict__ pa_in, const uint8_t* __restrict__ ok_in,
+__global__ void __launch_bounds__(BN_SYNC_MAX_BLOCK, 1) k_miller_table_sync(const AffG1* __restrict__ pa_in, const uint8_t* __restrict__ ok_in,
                                 const uint4* __restrict__ tab, Fq12* __restrict__ f_out, uint8_t* __restrict__ ok_out, size_t n) {
     size_t i = gtid();
     bool live = i < n;
@@ -417,7 +418,7 @@ BN_KERNEL k_miller_product_tables(const AffG1* __restrict__ pa, const uint8_t* _
 // every thread squares before every doubling coefficient but the first (a check without valid pairs squares 1) and runs
 // its own number of line multiplications between the barriers.
 template <int MAXV, int MAXS>
-__global__ void __launch_bounds__(BN_FEXP_BLOCK, 1) k_miller_product_sync(const AffG1* __restrict__ pa, const uint8_t* __restrict__ ok,
+__global__ void __launch_bounds__(BN_SYNC_MAX_BLOCK, 1) k_miller_product_sync(const AffG1* __restrict__ pa, const uint8_t* __restrict__ ok,
                                   const uint4* __restrict__ tabv, int v, const G1* __restrict__ g1s, const uint4* __restrict__ tabs, int m,
                                   Fq12* __restrict__ f_out, size_t n_checks) {
     size_t i = gtid();

@@ -19,8 +19,13 @@
 #if defined(__CUDACC__)
 namespace bn {
 
+// 7 slots (464-byte stride) for blocks of up to 448 threads, 6 slots (400 bytes = 25 x 16 B, odd as well) for 512-thread blocks:
+// 512 x 400 B = 205 KB.  The tower algorithms below use slots 0..5 only; the G2 line steps (bn_slots_curve.cuh) use all 7
+// and are launched with at most 448 threads.
 #define BN_NSLOTS 7
 #define BN_SLOT_STRIDE (BN_NSLOTS * 64 + 16)
+#define BN_SLOT_STRIDE6 (6 * 64 + 16)
+#define BN_SLOT_BLOCK7 448              /* largest block with 7 slots per thread */
 typedef uint32_t sp;   // shared-window byte address of one Fq2 slot
 
 __device__ __forceinline__ uint4 lds128(sp a) {
@@ -48,7 +53,8 @@ __device__ __forceinline__ void s_st(sp a, const Fq2& v) {
 }
 extern __shared__ uint4 bn_slot_mem[];
 __device__ __forceinline__ sp s_base() {
-    return (sp)__cvta_generic_to_shared(bn_slot_mem) + threadIdx.x * BN_SLOT_STRIDE;
+    const unsigned stride = blockDim.x > BN_SLOT_BLOCK7 ? BN_SLOT_STRIDE6 : BN_SLOT_STRIDE;
+    return (sp)__cvta_generic_to_shared(bn_slot_mem) + threadIdx.x * stride;
 }
 
 // ---- slot-to-slot Fq2 bodies (r may alias a or b) -------------------------------------------------------------
@@ -87,22 +93,18 @@ __device__ __forceinline__ Fq2& f6c(Fq6& a, int i) { return reinterpret_cast<Fq2
 //   p = 1: (t2, t3) = sqr4(z2, z3): z4' = 3 t2 - 2 z4, z5' = 3 t3 + 2 z5
 //   p = 2: (t4, t5) = sqr4(z4, z5): z3' = 3 t4 - 2 z3, z2' = 3 xi t5 + 2 z2
 // r must not overlap a.
-#ifndef BN_CYC_FUSED
-#define BN_CYC_FUSED 1
-#endif
-#if BN_CYC_FUSED
 // Two register-resident stages around the two products of one pair: the additive work of the Fq4 squaring and of
 // the 3t -+ 2z outputs never leaves registers, and the pair costs 4 calls instead of 17.
-// pre: slots A = a, B = b, S = a + b, T = a + xi b (operands read from local memory)
+// pre: slots 0 = a, 1 = b, 3 = S = a + b, 4 = T = a + xi b (operands read from local memory); slot 2 takes TMP = a b
 __device__ __noinline__ void s_cyc_pre(sp base, const Fq2& pa, const Fq2& pb) {
     Fq2 a = fq2_ld(pa), b = fq2_ld(pb), s, t;
     s_st(base, a); s_st(base + 64, b);
     fq_add(s.c0, a.c0, b.c0); fq_add(s.c1, a.c1, b.c1);
-    s_st(base + 320, s);
+    s_st(base + 192, s);
     fq_lin9<true>(t.c0, b.c0, b.c1);
     fq_lin9<false>(t.c1, b.c1, b.c0);
     fq_add(t.c0, t.c0, a.c0); fq_add(t.c1, t.c1, a.c1);
-    s_st(base + 384, t);
+    s_st(base + 256, t);
 }
 // out = 3 t - 2 z (minus) or 3 t + 2 z, every step reduced
 __device__ __forceinline__ void fq2_3t2z(Fq2& out, const Fq2& t, const Fq2& z, bool plus) {
@@ -115,7 +117,7 @@ __device__ __forceinline__ void fq2_3t2z(Fq2& out, const Fq2& t, const Fq2& z, b
 // post: with S = (a + b)(a + xi b) and TMP = a b in the slots: ta = S - TMP - xi TMP, tb = 2 TMP (times xi if xi_d);
 // out_c = 3 ta - 2 zc, out_d = 3 tb + 2 zd written to local memory
 __device__ __noinline__ void s_cyc_post(Fq2& out_c, Fq2& out_d, const Fq2& zc, const Fq2& zd, sp base, bool xi_d) {
-    Fq2 m = s_ld(base + 256), s = s_ld(base + 320), u, z;
+    Fq2 m = s_ld(base + 128), s = s_ld(base + 192), u, z;
     fq_lin9<true>(u.c0, m.c0, m.c1);
     fq_lin9<false>(u.c1, m.c1, m.c0);
     fq_sub(s.c0, s.c0, m.c0); fq_sub(s.c1, s.c1, m.c1);
@@ -135,32 +137,10 @@ __device__ __forceinline__ void s_cyc_pair(Fq12& r, const Fq12& a, int p, sp bas
     const int ic = p;
     const int id = (p == 0) ? 4 : (p == 1) ? 5 : 3;
     s_cyc_pre(base, f12c(a, ia), f12c(a, ib));
-    s_mul(base + 256, base, base + 64);             // TMP = a b
-    s_mul(base + 320, base + 320, base + 384);      // S = (a + b)(a + xi b)
+    s_mul(base + 128, base, base + 64);             // TMP = a b
+    s_mul(base + 192, base + 192, base + 256);      // S = (a + b)(a + xi b)
     s_cyc_post(f12c(r, ic), f12c(r, id), f12c(a, ic), f12c(a, id), base, p == 2);
 }
-#else
-__device__ __noinline__ void s_cyc_pair(Fq12& r, const Fq12& a, int p, sp base) {
-    const int ia = (p == 0) ? 0 : (p == 1) ? 3 : 1;
-    const int ib = (p == 0) ? 4 : (p == 1) ? 2 : 5;
-    const int ic = p;
-    const int id = (p == 0) ? 4 : (p == 1) ? 5 : 3;
-    const sp A = base, B = base + 64, C = base + 128, D = base + 192, TMP = base + 256, S = base + 320, T = base + 384;
-    s_in(A, f12c(a, ia)); s_in(B, f12c(a, ib)); s_in(C, f12c(a, ic)); s_in(D, f12c(a, id));
-    s_mul(TMP, A, B);                 // a b
-    s_xi(T, B); s_add(T, T, A);       // a + xi b
-    s_add(S, A, B);
-    s_mul(S, S, T);                   // (a + b)(a + xi b)
-    s_sub(S, S, TMP);
-    s_xi(T, TMP);
-    s_sub(S, S, T);                   // a^2 + xi b^2
-    s_dbl(TMP, TMP);                  // 2 a b
-    if (p == 2) s_xi(TMP, TMP);
-    s_sub(C, S, C); s_dbl(C, C); s_add(C, C, S);
-    s_add(D, TMP, D); s_dbl(D, D); s_add(D, D, TMP);
-    s_out(f12c(r, ic), C); s_out(f12c(r, id), D);
-}
-#endif
 __device__ __forceinline__ void s_cyclotomic_sqr_na(Fq12& r, const Fq12& a, sp base) {
     s_cyc_pair(r, a, 0, base);
     s_cyc_pair(r, a, 1, base);
@@ -221,23 +201,24 @@ __device__ __noinline__ void l_lin(Fq2& out, const Fq2& a, const Fq2& b, int mod
 }
 // out = a * b, operands and result in local memory, out not overlapping them.  post != 0 finishes an Fq12-level Karatsuba
 // product in the same pass: out_i = (a b)_i - (p_i + r_i) for post = 1, (a b)_i - (p_i - r_i) for post = 2.
-// Karatsuba (6 products) in three stages of 3 + 2 + 1 products on the 7 slots; 15 calls.
+// Karatsuba (6 products) in stages of 3 + 1 + 1 + 1 products on 6 slots (the first output leaves before the last product); 15 calls.
 __device__ __noinline__ void s_fq6_mul_p(Fq6& out, const Fq6& a, const Fq6& b, const Fq2& p0, const Fq2& r0, const Fq2& p1, const Fq2& r1,
                                          const Fq2& p2, const Fq2& r2, int post, sp base) {
-    const sp s0 = base, s1 = base + 64, s2 = base + 128, s3 = base + 192, s4 = base + 256, s5 = base + 320, s6 = base + 384;
+    const sp s0 = base, s1 = base + 64, s2 = base + 128, s3 = base + 192, s4 = base + 256, s5 = base + 320;
     s_prep1(a.c0, a.c1, s0, s2, s4);
     s_prep1(b.c0, b.c1, s1, s3, s5);
     s_mul(s0, s0, s1);                       // v0 = a0 b0
     s_mul(s2, s2, s3);                       // v1 = a1 b1
     s_mul(s4, s4, s5);                       // (a0 + a1)(b0 + b1)
-    s_prep1(a.c1, a.c2, BN_SKIP, s1, s5);
-    s_prep1(b.c1, b.c2, BN_SKIP, s3, s6);
+    s_in(s1, a.c2); s_in(s3, b.c2);
     s_mul(s1, s1, s3);                       // v2 = a2 b2
-    s_mul(s5, s5, s6);                       // (a1 + a2)(b1 + b2)
+    s_prep1(a.c1, a.c2, BN_SKIP, BN_SKIP, s3);
+    s_prep1(b.c1, b.c2, BN_SKIP, BN_SKIP, s5);
+    s_mul(s3, s3, s5);                       // (a1 + a2)(b1 + b2)
+    s_f6_out(out.c0, s3, s2, s1, s0, 0, p0, r0, post);    // v0 + xi ((a1+a2)(b1+b2) - v1 - v2); frees slot 3
     s_prep1(a.c0, a.c2, BN_SKIP, BN_SKIP, s3);
-    s_prep1(b.c0, b.c2, BN_SKIP, BN_SKIP, s6);
-    s_mul(s3, s3, s6);                       // (a0 + a2)(b0 + b2)
-    s_f6_out(out.c0, s5, s2, s1, s0, 0, p0, r0, post);    // v0 + xi ((a1+a2)(b1+b2) - v1 - v2)
+    s_prep1(b.c0, b.c2, BN_SKIP, BN_SKIP, s5);
+    s_mul(s3, s3, s5);                       // (a0 + a2)(b0 + b2)
     s_f6_out(out.c1, s4, s0, s2, s1, 1, p1, r1, post);    // (a0+a1)(b0+b1) - v0 - v1 + xi v2
     s_f6_out(out.c2, s3, s0, s1, s2, 2, p2, r2, post);    // (a0+a2)(b0+b2) - v0 - v2 + v1
 }

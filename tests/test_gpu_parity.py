@@ -406,7 +406,7 @@ def test_pairing_across_table_chunk_boundary(eng):
     assert (out[a] == out[b]).all()
 
 
-@pytest.mark.parametrize("n", [1, 63, 449, 1000])
+@pytest.mark.parametrize("n", [1, 63, 449, 1000, 1600])
 def test_slot_file_and_local_memory_paths_agree(eng, n):
     """The slot-file kernels (one 448-thread block per SM with phase barriers: k_miller_table_sync, k_final_exp_hard_sync),
     the 64-thread slot-file hard part and the local-memory kernels produce the oracle's bytes at batch sizes below, at and
@@ -422,7 +422,8 @@ def test_slot_file_and_local_memory_paths_agree(eng, n):
     exp_f, exp_ok = c.miller_loop_many(g2[:m * G2], g1[:m * G1])
     ref = eng.pairing(g1, g2)
     assert ref[:m * GT].tobytes() == exp.tobytes()
-    for env in ({"BN254_FEXP_SMEM": "0", "BN254_MILLER_SMEM": "0", "BN254_LINES_SMEM": "0"}, {"BN254_FEXP_SMEM": "1"}, {"BN254_FEXP_SMEM": "2", "BN254_MILLER_SMEM": "1"}):
+    for env in ({"BN254_FEXP_SMEM": "0", "BN254_MILLER_SMEM": "0", "BN254_LINES_SMEM": "0"}, {"BN254_FEXP_SMEM": "1"}, {"BN254_FEXP_SMEM": "2", "BN254_MILLER_SMEM": "1"},
+                {"BN254_BIG_BLOCKS": "2"}):   # 512-thread blocks on 6 slots per thread (otherwise chosen from 2^19 pairings up)
         os.environ.update(env)
         try:
             e2 = bn.Engine(0)
