@@ -449,7 +449,9 @@ int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_
     CU(cudaEventRecord(ctx->ev_fork, main_stream));
     CU(cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
     ctx->ws_ovr = ws; ctx->ws_ovr_bytes = wA;
-    ctx->force_block = BN_FEXP_BLOCK;   // each half on its own SMs: two smaller blocks per SM would interleave their phases
+    // one-wave batches: each half on its own SMs with full blocks (two smaller blocks per SM would interleave their phases);
+    // larger batches fill every SM with one block at a time anyway and keep the block size rule of sync_block
+    if (n <= (size_t)ctx->sms * BN_FEXP_BLOCK) ctx->force_block = BN_FEXP_BLOCK;
     int rc = pairing_many_enqueue(ctx, (const char*)g1, (const char*)g2, (char*)gt_out, mapped, d, 0, nA);
     if (rc == 0) {
         ctx->stream = ctx->stream2;
