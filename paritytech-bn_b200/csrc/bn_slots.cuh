@@ -262,12 +262,22 @@ __device__ __noinline__ void s_fq12_sqr_na(Fq12& r, const Fq12& a, sp base) {
 // zi), x from the slots xbase + 64 * index (packed in xi).  Same IMAD work as the 13-product Karatsuba form, no additive glue.
 __device__ __noinline__ void s_dot3(Fq2& out, const Fq12& f, uint32_t zi, sp xbase, uint32_t xi) {
     FqWide t0, t1, s;
-#pragma unroll
-    for (int i = 0; i < 16; i++) { t0.v[i] = 0; t1.v[i] = 0; s.v[i] = 0; }
+    Fq2 z = fq2_ld(f12c(f, zi & 7));
+    {   // first term: plain products
+        Fq2 x = s_ld(xbase + 64 * (xi & 7));
+        Fq2 zn = fq2_ld(f12c(f, (zi >> 3) & 7));      // next coefficient: its local-memory latency rides under the products
+        fq_mulwide(t0, z.c0, x.c0);
+        fq_mulwide(t1, z.c1, x.c1);
+        Fq sa, sb;
+        fq_add_noreduce(sa, z.c0, z.c1);
+        fq_add_noreduce(sb, x.c0, x.c1);
+        fq_mulwide(s, sa, sb);
+        z = zn;
+    }
 #pragma unroll 1
-    for (int k = 0; k < 3; k++) {
-        Fq2 z = fq2_ld(f12c(f, (zi >> (3 * k)) & 7));
+    for (int k = 1; k < 3; k++) {
         Fq2 x = s_ld(xbase + 64 * ((xi >> (3 * k)) & 7));
+        Fq2 zn = fq2_ld(f12c(f, (zi >> (3 * (k < 2 ? k + 1 : k))) & 7));
         FqWide p;
         fq_mulwide(p, z.c0, x.c0); wide_add(t0, p);
         fq_mulwide(p, z.c1, x.c1); wide_add(t1, p);
@@ -275,6 +285,7 @@ __device__ __noinline__ void s_dot3(Fq2& out, const Fq12& f, uint32_t zi, sp xba
         fq_add_noreduce(sa, z.c0, z.c1);
         fq_add_noreduce(sb, x.c0, x.c1);
         fq_mulwide(p, sa, sb); wide_add(s, p);
+        z = zn;
     }
     wide_sub(s, t0);                 // never borrows
     wide_sub(s, t1);
