@@ -199,6 +199,27 @@ __device__ __noinline__ void l_lin(Fq2& out, const Fq2& a, const Fq2& b, int mod
     else { fq_add(x.c0, x.c0, y.c0); fq_add(x.c1, x.c1, y.c1); }
     fq2_st(out, x);
 }
+// The same over the three coefficients of an Fq6 in one call: out = a +- b, or a +- v b with rot (v b = (xi b2, b0, b1),
+// src/fields/fq6.rs:109-115).  The operands of the next coefficient are loaded before the current one is computed, so the
+// call exposes one local-memory latency instead of three.  out must not overlap a or b.
+__device__ __noinline__ void l_lin6(Fq6& out, const Fq6& a, const Fq6& b, int mode, bool rot) {
+    Fq2 x = fq2_ld(a.c0), y = fq2_ld(rot ? b.c2 : b.c0);
+#pragma unroll 1
+    for (int i = 0; i < 3; i++) {
+        const int n = i < 2 ? i + 1 : 2;
+        Fq2 xn = fq2_ld(f6c(a, n)), yn = fq2_ld(f6c(b, rot ? n - 1 : n));
+        if (rot && i == 0) {
+            Fq2 t;
+            fq_lin9<true>(t.c0, y.c0, y.c1);
+            fq_lin9<false>(t.c1, y.c1, y.c0);
+            y = t;
+        }
+        if (mode & BN_LIN_SUB) { fq_sub(x.c0, x.c0, y.c0); fq_sub(x.c1, x.c1, y.c1); }
+        else { fq_add(x.c0, x.c0, y.c0); fq_add(x.c1, x.c1, y.c1); }
+        fq2_st(f6c(out, i), x);
+        x = xn; y = yn;
+    }
+}
 // out = a * b, operands and result in local memory, out not overlapping them.  post != 0 finishes an Fq12-level Karatsuba
 // product in the same pass: out_i = (a b)_i - (p_i + r_i) for post = 1, (a b)_i - (p_i - r_i) for post = 2.
 // Karatsuba (6 products) in stages of 3 + 1 + 1 + 1 products on 6 slots (the first output leaves before the last product); 15 calls.
@@ -232,13 +253,11 @@ __device__ __noinline__ void s_fq12_mul_na(Fq12& r, const Fq12& a, const Fq12& b
     s_fq6_mul(aa, a.c0, b.c0, aa, aa, 0, base);
     s_fq6_mul(bb, a.c1, b.c1, bb, bb, 0, base);
     // r.c0 doubles as the buffer of a0 + a1; c1 = (a0 + a1)(b0 +- b1) - (aa +- bb)
-    l_lin(r.c0.c0, a.c0.c0, a.c1.c0, BN_LIN_ADD); l_lin(r.c0.c1, a.c0.c1, a.c1.c1, BN_LIN_ADD); l_lin(r.c0.c2, a.c0.c2, a.c1.c2, BN_LIN_ADD);
-    l_lin(sb.c0, b.c0.c0, b.c1.c0, m); l_lin(sb.c1, b.c0.c1, b.c1.c1, m); l_lin(sb.c2, b.c0.c2, b.c1.c2, m);
+    l_lin6(r.c0, a.c0, a.c1, BN_LIN_ADD, false);
+    l_lin6(sb, b.c0, b.c1, m, false);
     s_fq6_mul(r.c1, r.c0, sb, aa, bb, conj_b ? 2 : 1, base);
     // c0 = aa +- v bb, v (b0, b1, b2) = (xi b2, b0, b1)
-    l_lin(r.c0.c0, aa.c0, bb.c2, m | BN_LIN_XI);
-    l_lin(r.c0.c1, aa.c1, bb.c0, m);
-    l_lin(r.c0.c2, aa.c2, bb.c1, m);
+    l_lin6(r.c0, aa, bb, m, true);
 }
 // r = a^2, complex method (value of src/fields/fq12.rs:295-303): ab = a0 a1, c0 = (a0 + a1)(a0 + v a1) - ab - v ab, c1 = 2 ab.
 // r must not overlap a.
@@ -247,11 +266,11 @@ __device__ __noinline__ void s_fq12_sqr_na(Fq12& r, const Fq12& a, sp base) {
     Fq2 xab2;
     s_fq6_mul(ab, a.c0, a.c1, ab, ab, 0, base);
     // r.c1 doubles as the buffer of a0 + a1
-    l_lin(r.c1.c0, a.c0.c0, a.c1.c0, BN_LIN_ADD); l_lin(r.c1.c1, a.c0.c1, a.c1.c1, BN_LIN_ADD); l_lin(r.c1.c2, a.c0.c2, a.c1.c2, BN_LIN_ADD);
-    l_lin(sv.c0, a.c0.c0, a.c1.c2, BN_LIN_XI); l_lin(sv.c1, a.c0.c1, a.c1.c0, BN_LIN_ADD); l_lin(sv.c2, a.c0.c2, a.c1.c1, BN_LIN_ADD);
+    l_lin6(r.c1, a.c0, a.c1, BN_LIN_ADD, false);
+    l_lin6(sv, a.c0, a.c1, BN_LIN_ADD, true);
     l_lin(xab2, ab.c2, ab.c2, BN_LIN_XI | BN_LIN_ZERO_A);
     s_fq6_mul_p(r.c0, r.c1, sv, ab.c0, xab2, ab.c1, ab.c0, ab.c2, ab.c1, 1, base);
-    l_lin(r.c1.c0, ab.c0, ab.c0, BN_LIN_ADD); l_lin(r.c1.c1, ab.c1, ab.c1, BN_LIN_ADD); l_lin(r.c1.c2, ab.c2, ab.c2, BN_LIN_ADD);
+    l_lin6(r.c1, ab, ab, BN_LIN_ADD, false);
 }
 
 // ---- line multiplication as six 3-term dot products (value of src/fields/fq12.rs:130-196) ----------------------
