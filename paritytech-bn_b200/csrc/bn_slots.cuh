@@ -157,6 +157,17 @@ __device__ __noinline__ void s_prep1(const Fq2& pi, const Fq2& pj, sp dI, sp dJ,
     fq_add(s.c0, x.c0, y.c0); fq_add(s.c1, x.c1, y.c1);
     s_st(dS, s);
 }
+// both sides of a stage in one call (all four operands loaded before the first addition: one local-memory latency):
+// slots dI <- a_i, dI + 64 <- b_i, dJ <- a_j, dJ + 64 <- b_j (each pair skipped when BN_SKIP), dSA <- a_i + a_j, dSB <- b_i + b_j
+__device__ __noinline__ void s_prep2(const Fq2& ai, const Fq2& aj, const Fq2& bi, const Fq2& bj, sp dI, sp dJ, sp dSA, sp dSB) {
+    Fq2 x = fq2_ld(ai), y = fq2_ld(aj), u = fq2_ld(bi), w = fq2_ld(bj), s;
+    if (dI != BN_SKIP) { s_st(dI, x); s_st(dI + 64, u); }
+    if (dJ != BN_SKIP) { s_st(dJ, y); s_st(dJ + 64, w); }
+    fq_add(s.c0, x.c0, y.c0); fq_add(s.c1, x.c1, y.c1);
+    s_st(dSA, s);
+    fq_add(s.c0, u.c0, w.c0); fq_add(s.c1, u.c1, w.c1);
+    s_st(dSB, s);
+}
 // one output coefficient: t = Q - Va - Vb; kind 0: xi t + Vc, kind 1: t + xi Vc, kind 2: t + Vc; then minus (aa + bb) for
 // post = 1, minus (aa - bb) for post = 2 (the Fq12-level Karatsuba correction, operands in local memory); result to local memory
 __device__ __noinline__ void s_f6_out(Fq2& out, sp Q, sp Va, sp Vb, sp Vc, int kind, const Fq2& aa, const Fq2& bb, int post) {
@@ -226,19 +237,16 @@ __device__ __noinline__ void l_lin6(Fq6& out, const Fq6& a, const Fq6& b, int mo
 __device__ __noinline__ void s_fq6_mul_p(Fq6& out, const Fq6& a, const Fq6& b, const Fq2& p0, const Fq2& r0, const Fq2& p1, const Fq2& r1,
                                          const Fq2& p2, const Fq2& r2, int post, sp base) {
     const sp s0 = base, s1 = base + 64, s2 = base + 128, s3 = base + 192, s4 = base + 256, s5 = base + 320;
-    s_prep1(a.c0, a.c1, s0, s2, s4);
-    s_prep1(b.c0, b.c1, s1, s3, s5);
+    s_prep2(a.c0, a.c1, b.c0, b.c1, s0, s2, s4, s5);
     s_mul(s0, s0, s1);                       // v0 = a0 b0
     s_mul(s2, s2, s3);                       // v1 = a1 b1
     s_mul(s4, s4, s5);                       // (a0 + a1)(b0 + b1)
     s_in(s1, a.c2); s_in(s3, b.c2);
     s_mul(s1, s1, s3);                       // v2 = a2 b2
-    s_prep1(a.c1, a.c2, BN_SKIP, BN_SKIP, s3);
-    s_prep1(b.c1, b.c2, BN_SKIP, BN_SKIP, s5);
+    s_prep2(a.c1, a.c2, b.c1, b.c2, BN_SKIP, BN_SKIP, s3, s5);
     s_mul(s3, s3, s5);                       // (a1 + a2)(b1 + b2)
     s_f6_out(out.c0, s3, s2, s1, s0, 0, p0, r0, post);    // v0 + xi ((a1+a2)(b1+b2) - v1 - v2); frees slot 3
-    s_prep1(a.c0, a.c2, BN_SKIP, BN_SKIP, s3);
-    s_prep1(b.c0, b.c2, BN_SKIP, BN_SKIP, s5);
+    s_prep2(a.c0, a.c2, b.c0, b.c2, BN_SKIP, BN_SKIP, s3, s5);
     s_mul(s3, s3, s5);                       // (a0 + a2)(b0 + b2)
     s_f6_out(out.c1, s4, s0, s2, s1, 1, p1, r1, post);    // (a0+a1)(b0+b1) - v0 - v1 + xi v2
     s_f6_out(out.c2, s3, s0, s1, s2, 2, p2, r2, post);    // (a0+a2)(b0+b2) - v0 - v2 + v1
