@@ -117,19 +117,18 @@ __device__ __forceinline__ void fq2_3t2z(Fq2& out, const Fq2& t, const Fq2& z, b
 // post: with S = (a + b)(a + xi b) and TMP = a b in the slots: ta = S - TMP - xi TMP, tb = 2 TMP (times xi if xi_d);
 // out_c = 3 ta - 2 zc, out_d = 3 tb + 2 zd written to local memory
 __device__ __noinline__ void s_cyc_post(Fq2& out_c, Fq2& out_d, const Fq2& zc, const Fq2& zd, sp base, bool xi_d) {
-    Fq2 m = s_ld(base + 128), s = s_ld(base + 192), u, z;
+    Fq2 z = fq2_ld(zc), w = fq2_ld(zd);                      // both old coefficients up front: one local-memory latency
+    Fq2 m = s_ld(base + 128), s = s_ld(base + 192), u;
     fq_lin9<true>(u.c0, m.c0, m.c1);
     fq_lin9<false>(u.c1, m.c1, m.c0);
     fq_sub(s.c0, s.c0, m.c0); fq_sub(s.c1, s.c1, m.c1);
     fq_sub(s.c0, s.c0, u.c0); fq_sub(s.c1, s.c1, u.c1);      // ta
-    z = fq2_ld(zc);
     fq2_3t2z(z, s, z, false);
     fq2_st(out_c, z);
     if (xi_d) { fq_dbl(m.c0, u.c0); fq_dbl(m.c1, u.c1); }    // xi (2 TMP) = 2 (xi TMP)
     else { fq_dbl(m.c0, m.c0); fq_dbl(m.c1, m.c1); }         // tb
-    z = fq2_ld(zd);
-    fq2_3t2z(z, m, z, true);
-    fq2_st(out_d, z);
+    fq2_3t2z(w, m, w, true);
+    fq2_st(out_d, w);
 }
 __device__ __forceinline__ void s_cyc_pair(Fq12& r, const Fq12& a, int p, sp base) {
     const int ia = (p == 0) ? 0 : (p == 1) ? 3 : 1;
