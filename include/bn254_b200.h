@@ -15,12 +15,25 @@
  *            = 16,832 B, field order of src/groups/mod.rs:566-577
  *
  * Every entry point is batched (pointer + count); the scalar functions of src/lib.rs are the n = 1
- * calls.  Host-pointer entry points are synchronous.  `*_dev` entry points take DEVICE pointers
- * (16-byte aligned) and enqueue on the context's stream without synchronising.
+ * calls.  Host-pointer entry points are synchronous: they stage through the context's grow-only device
+ * arenas (no cudaMalloc on the steady-state path) and return when the results are in the caller's
+ * buffers.  `*_dev` entry points take DEVICE pointers (16-byte aligned, checked: BN254_ERR_ARG otherwise)
+ * and enqueue on the context's stream.  They do not synchronise, with two documented exceptions:
+ *   - the first call that needs a larger workspace than any call before it grows the arena
+ *     (cudaStreamSynchronize + cudaFree + cudaMalloc, once);
+ *   - bn254_pairing_product_*_dev with a NULL d_gt_out synchronise before returning (the temporary that
+ *     receives the Gt values comes from the arena and must not be reused by the next call too early).
+ * Limits of the product entry points: at most 8 shared G2Precomp tables per check; more than 8 variable
+ * pairs per check cannot be combined with shared tables.
+ *
+ * Threading: a context is ONE device, two streams and three arenas.  Every entry point locks the
+ * context for its duration, so concurrent callers of one context are safe but serialise; use one
+ * context per host thread (or per GPU) for concurrency.  bn254_last_error() is thread-local.
  *
  * Return codes: 0 = ok; > 0 = reference-level condition (documented per function);
  *               < 0 = runtime failure (-1 bad argument, -2 CUDA error, -3 out of memory).
- * Nothing aborts or throws across this boundary.  There is NO CPU fallback: without a CUDA device
+ * Nothing aborts or throws across this boundary (C++ exceptions are caught inside and mapped to
+ * BN254_ERR_NOMEM / BN254_ERR_CUDA).  There is NO CPU fallback: without a CUDA device
  * bn254_ctx_create fails and nothing else can be called.
  */
 #ifndef BN254_B200_H
@@ -53,7 +66,30 @@ typedef struct bn254_g2precomp bn254_g2precomp; /* device-resident G2Precomp tab
                                                    the reference's G2Precomp is private, src/lib.rs:7) */
 
 /* ---- context ------------------------------------------------------------------------------- */
+/* Runtime switches of a context as plain data (no hidden global state).  -1 in any field = the
+ * library default; bn254_ctx_options_default() fills the struct with the defaults, letting the BN254_*
+ * environment variables named below override them (A/B runs without recompiling).  bn254_ctx_create(d, out)
+ * is bn254_ctx_create_ex(d, NULL, out), i.e. exactly those defaults. */
+typedef struct bn254_ctx_options {
+    uint32_t struct_size;  /* sizeof(bn254_ctx_options) of the caller's header (forward compatibility) */
+    int32_t pipeline;      /* BN254_PIPELINE      1: host-buffer pairing path overlaps copies with kernels */
+    int32_t big_blocks;    /* BN254_BIG_BLOCKS    1: 512-thread blocks when they save waves; 2: for every batch > 512 (tests) */
+    int32_t fused_miller;  /* BN254_FUSED_MILLER  0: affine -> line table -> Miller from table; 1: one fused kernel (A/B) */
+    int32_t split_fexp;    /* BN254_SPLIT_FEXP    with fexp_smem = 0: 1 = easy + hard kernels, 0 = one kernel */
+    int32_t fexp_smem;     /* BN254_FEXP_SMEM     2: hard part on the slot file, one phase-synchronised block per SM; 1: 64-thread blocks; 0: local memory */
+    int32_t miller_smem;   /* BN254_MILLER_SMEM   1: Miller loop from the table on the slot file; 0: local memory */
+    int32_t lines_smem;    /* BN254_LINES_SMEM    1: G2 line tables on the slot file (one-wave batches); 0: local memory */
+    int32_t subgroup_ref;  /* BN254_SUBGROUP_REF  0: G2 order check by the psi test; 1: the reference's [r-1]P + P ladder.
+                              Both decide the same predicate; this picks the algorithm that validates untrusted input. */
+    int32_t zerocopy_out;  /* BN254_ZEROCOPY_OUT  1: pinned (mapped) output buffers are written by the last kernel directly */
+    int32_t coop_max_n;    /* BN254_COOP_MAX_N    batches of at most this many pairings take the warp-cooperative latency path
+                              (one warp per pairing); 0 disables it */
+    int32_t stack_bytes;   /* BN254_STACK_BYTES   0: leave cudaLimitStackSize alone (the driver sizes static call graphs itself);
+                              > 0: raise the DEVICE-WIDE limit to at least this (affects the embedding process) */
+} bn254_ctx_options;
+void bn254_ctx_options_default(bn254_ctx_options* opt);
 int bn254_ctx_create(int device, bn254_ctx** out);
+int bn254_ctx_create_ex(int device, const bn254_ctx_options* opt, bn254_ctx** out);
 void bn254_ctx_destroy(bn254_ctx* ctx);
 int bn254_ctx_device(const bn254_ctx* ctx);
 /* the CUDA stream (cudaStream_t) all work of this context is enqueued on */
@@ -68,10 +104,17 @@ const char* bn254_build_info(void);
 /* A pair with either point at infinity yields Gt::one() (src/groups/mod.rs:896). */
 int bn254_pairing_many(bn254_ctx* ctx, const void* g1, const void* g2, void* gt_out, size_t n);
 int bn254_pairing_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_g2, void* d_gt_out, size_t n);
+/* The same over a device list (SURVEY 8b "device-list argument", 8e): ONE call, n independent pairs in one host
+ * buffer, contiguous index ranges [n*d/n_ctx, n*(d+1)/n_ctx) on contexts ctxs[0..n_ctx) (one per GPU; several
+ * contexts on one GPU are allowed), one host thread and stream pair per device, every result written to the caller's
+ * own index range of gt_out.  No data-path collective: the pairs are independent.  Pinned (cudaHostAlloc /
+ * cudaHostRegister) buffers make the copies asynchronous; pageable buffers work and are staged by the driver. */
+int bn254_pairing_many_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1, const void* g2, void* gt_out, size_t n);
 
 /* Profiling twin of bn254_pairing_many_dev: identical launches, each kernel bracketed by CUDA events on the
- * context's stream.  ms[4] = {affine conversion, G2 line table, Miller loop from table, final exponentiation}
- * in milliseconds (fused-Miller build: ms[0] = ms[1] = 0, ms[2] = the fused kernel).  Synchronises. */
+ * context's stream.  ms[5] = {affine conversion, G2 line table, Miller loop from table, easy part of the final
+ * exponentiation, hard part} in milliseconds (fused-Miller option: ms[0] = ms[1] = 0, ms[2] = the fused kernel;
+ * single-kernel final exponentiation: ms[3] = 0, ms[4] = that kernel).  Synchronises. */
 int bn254_pairing_many_dev_timed(bn254_ctx* ctx, const void* d_g1, const void* d_g2, void* d_gt_out, size_t n, float* ms);
 
 /* ---- pairing_batch: src/lib.rs:615-623 `pairing_batch(&[(G1, G2)]) -> Gt` ---------------------- */
@@ -115,6 +158,15 @@ int bn254_g1_mul_many(bn254_ctx* ctx, const void* g1, const void* fr, void* g1_o
 int bn254_g2_mul_many(bn254_ctx* ctx, const void* g2, const void* fr, void* g2_out, size_t n);
 int bn254_g1_mul_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_fr, void* d_out, size_t n);
 int bn254_g2_mul_many_dev(bn254_ctx* ctx, const void* d_g2, const void* d_fr, void* d_out, size_t n);
+/* (p * k).normalize() in one call for callers that normalise anyway (src/lib.rs:425-431 followed by :391-398): a signed
+ * 4-bit window with uniform control flow (64 table additions instead of the ~254 a warp executes on the bit-serial
+ * ladder).  Normalised coordinates are unique, so the bytes equal the reference's; a result at infinity (k = 0, p at
+ * infinity, or a non-member whose multiple vanishes) is recomputed with the reference's own ladder so that even those
+ * bytes match. */
+int bn254_g1_mul_normalized_many(bn254_ctx* ctx, const void* g1, const void* fr, void* g1_out, size_t n);
+int bn254_g2_mul_normalized_many(bn254_ctx* ctx, const void* g2, const void* fr, void* g2_out, size_t n);
+int bn254_g1_mul_normalized_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_fr, void* d_out, size_t n);
+int bn254_g2_mul_normalized_many_dev(bn254_ctx* ctx, const void* d_g2, const void* d_fr, void* d_out, size_t n);
 /* Group::normalize, src/lib.rs:391-398, :542-549: z -> one (infinity untouched) */
 int bn254_g1_normalize_many(bn254_ctx* ctx, const void* g1, void* g1_out, size_t n);
 int bn254_g2_normalize_many(bn254_ctx* ctx, const void* g2, void* g2_out, size_t n);
@@ -174,6 +226,14 @@ int bn254_pairing_product_precomp_many_dev(bn254_ctx* ctx, const bn254_g2precomp
  * ctxs[0] by peer copy, multiplied, and exponentiated once.  Same skip semantics as pairing_batch. */
 int bn254_pairing_product_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1, const void* g2, size_t n,
                                   void* gt_out, uint8_t* is_one);
+/* Same with the phases timed on the host clock (extra synchronisations, for bench.py): phase_ms[0] = copies in + Miller
+ * partial products on all devices (wall, i.e. max over devices), [1] = gather of the n_ctx 384-byte partials to ctxs[0]
+ * (peer copies), [2] = product of the partials + the one final exponentiation + result copy. */
+int bn254_pairing_product_sharded_timed(bn254_ctx** ctxs, size_t n_ctx, const void* g1, const void* g2, size_t n,
+                                        void* gt_out, uint8_t* is_one, double* phase_ms);
+/* Device-resident twin of bn254_miller_product: d_gt_out receives the un-exponentiated product of n pairs already in
+ * HBM (asynchronous on the context's stream).  The per-rank step of a product sharded over processes. */
+int bn254_miller_product_dev(bn254_ctx* ctx, const void* d_g1, const void* d_g2, size_t n, void* d_gt_out);
 
 /* ---- field-level test hooks (parity tests of the arithmetic kernels) ---------------------------- */
 /* op: 0 = Fq mul, 1 = Fq add, 2 = Fq sub, 3 = Fq2 mul, 4 = Fq2 sqr, 5 = Fq6 mul, 6 = Fq12 mul,

@@ -11,25 +11,47 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "_build", "libbn254_oracle.so")
+# bench.py's CPU legs set BN254_ORACLE_NATIVE=1: the library is then compiled ON the machine that times it with -march=native
+#  instead of the portable x86-64-v3 build that travels with the snapshot.
+_SO_NATIVE = os.path.join(_HERE, "_build", "libbn254_oracle_native.so")
+NATIVE_CFLAGS = "-O3 -march=native -fopenmp -fPIC -Wall -Wextra -Wno-unused-function"
 
 FQ, FR, FQ2, FQ6, FQ12 = 32, 32, 64, 192, 384
 G1, G2, ELL = 96, 192, 192
 G2PRECOMP = 128 + 87 * 192
 
 
-def build(force=False):
+def build(force=False, native=False):
     """Compile the oracle if missing or stale.  Serialised with a lock file and installed by an atomic rename, so
-    concurrent processes (the two ranks of the gloo test on a fresh checkout) never load a half-written library."""
+    concurrent processes (the two ranks of the gloo test on a fresh checkout) never load a half-written library.
+    native=True: a second library built with -march=native on this very machine (always rebuilt when the host differs:
+    the marker file records the CPU model it was built on)."""
     import fcntl
     src = os.path.join(_HERE, "bn254_oracle.c")
-    os.makedirs(os.path.dirname(_SO), exist_ok=True)
-    with open(os.path.join(os.path.dirname(_SO), ".lock"), "w") as lk:
+    so = _SO_NATIVE if native else _SO
+    os.makedirs(os.path.dirname(so), exist_ok=True)
+    with open(os.path.join(os.path.dirname(so), ".lock"), "w") as lk:
         fcntl.flock(lk, fcntl.LOCK_EX)
-        if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
-            tmp = "%s.tmp.%d" % (_SO, os.getpid())
-            subprocess.check_call(["make", "-s", "-C", _HERE, "OUT=" + tmp] + (["-B"] if force else []))
-            os.replace(tmp, _SO)
-    return _SO
+        stale = force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src)
+        marker, cpu = so + ".cpu", ""
+        if native:
+            try:
+                cpu = [ln for ln in open("/proc/cpuinfo") if ln.startswith(("model name", "flags"))][:2]
+                cpu = "".join(cpu)
+            except OSError:
+                pass
+            stale = stale or not os.path.exists(marker) or open(marker).read() != cpu
+        if stale:
+            tmp = "%s.tmp.%d" % (so, os.getpid())
+            cmd = ["make", "-s", "-B", "-C", _HERE, "OUT=" + tmp]
+            if native:
+                cmd.append("CFLAGS=" + NATIVE_CFLAGS)
+            subprocess.check_call(cmd)
+            os.replace(tmp, so)
+            if native:
+                with open(marker, "w") as f:
+                    f.write(cpu)
+    return so
 
 
 _lib = None
@@ -38,8 +60,16 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
-        build()
-        _lib = ctypes.CDLL(_SO)
+        so = None
+        if os.environ.get("BN254_ORACLE_NATIVE") == "1":
+            try:
+                so = build(native=True)
+            except Exception:
+                so = None          # no compiler on this machine: the portable build below
+        if so is None:
+            so = build()
+        _lib = ctypes.CDLL(so)
+        _lib.build_flavour = "native" if so == _SO_NATIVE else "x86-64-v3"
         _lib.orc_init()
         _lib.orc_g2precomp_size.restype = ctypes.c_size_t
         assert _lib.orc_g2precomp_size() == G2PRECOMP

@@ -63,9 +63,18 @@ def load_library(variant=None):
 
 
 def _arr(a, unit):
+    """Byte view of a buffer of `unit`-byte elements.  Arrays of wider integers (the natural uint32/uint64 limb layout of a
+    U256) are REINTERPRETED as their little-endian bytes, never value-cast; anything that is not an integer array is refused."""
     if isinstance(a, (bytes, bytearray, memoryview)):
         a = np.frombuffer(bytes(a), dtype=np.uint8)
-    a = np.ascontiguousarray(a, dtype=np.uint8).reshape(-1)
+    a = np.asarray(a)
+    if a.dtype != np.uint8:
+        if a.dtype.kind not in "ui":
+            raise TypeError("expected a byte buffer or an integer limb array, got dtype %s" % a.dtype)
+        if a.dtype.byteorder == ">":
+            raise TypeError("big-endian limb arrays are not the crate's memory image")
+        a = np.ascontiguousarray(a).view(np.uint8)
+    a = np.ascontiguousarray(a).reshape(-1)
     if a.size % unit:
         raise ValueError("buffer of %d bytes is not a whole number of %d-byte elements" % (a.size, unit))
     return a, a.size // unit
@@ -73,6 +82,31 @@ def _arr(a, unit):
 
 def _p(a):
     return a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+
+
+def _out(out, nbytes):
+    """Caller-owned result buffer (e.g. pinned memory) or a fresh array."""
+    if out is None:
+        return np.empty(nbytes, dtype=np.uint8)
+    assert out.dtype == np.uint8 and out.size == nbytes and out.flags["C_CONTIGUOUS"]
+    return out
+
+
+class CtxOptions(ctypes.Structure):
+    """bn254_ctx_options (include/bn254_b200.h): -1 = library default."""
+    _fields_ = [("struct_size", ctypes.c_uint32)] + [(k, ctypes.c_int32) for k in (
+        "pipeline", "big_blocks", "fused_miller", "split_fexp", "fexp_smem", "miller_smem", "lines_smem", "subgroup_ref",
+        "zerocopy_out", "coop_max_n", "stack_bytes")]
+
+    def __init__(self, **kw):
+        super().__init__()
+        self.struct_size = ctypes.sizeof(CtxOptions)
+        for k, _ in self._fields_[1:]:
+            setattr(self, k, -1)
+        for k, v in kw.items():
+            if k not in dict(self._fields_):
+                raise KeyError("unknown context option %r" % k)
+            setattr(self, k, int(v))
 
 
 class G2Precomp:
@@ -104,10 +138,16 @@ class G2Precomp:
 class Engine:
     """One CUDA device + stream (bn254_ctx)."""
 
-    def __init__(self, device=0, variant=None):
+    def __init__(self, device=0, variant=None, **options):
+        """options: fields of bn254_ctx_options (e.g. fexp_smem=0, big_blocks=2, coop_max_n=0); unset fields keep the
+        library defaults (which the BN254_* environment variables may override)."""
         self.lib = load_library(variant)
         self.ctx = ctypes.c_void_p()
-        rc = self.lib.bn254_ctx_create(ctypes.c_int(device), ctypes.byref(self.ctx))
+        if options:
+            opt = CtxOptions(**options)
+            rc = self.lib.bn254_ctx_create_ex(ctypes.c_int(device), ctypes.byref(opt), ctypes.byref(self.ctx))
+        else:
+            rc = self.lib.bn254_ctx_create(ctypes.c_int(device), ctypes.byref(self.ctx))
         if rc != 0:
             raise BnError("bn254_ctx_create(%d) failed: %s" % (device, self.lib.bn254_last_error().decode()))
         self.device = device
@@ -156,7 +196,7 @@ class Engine:
         self._check(self.lib.bn254_pairing_many(self.ctx, _p(g1), _p(g2), _p(out), ctypes.c_size_t(n)))
         return out
 
-    def pairing_batch(self, g1, g2, pairs_per_check=None):
+    def pairing_batch(self, g1, g2, pairs_per_check=None, out=None, is_one=None):
         """pairing_batch (src/lib.rs:615-623).  With pairs_per_check: many independent checks.
         Returns (Gt images, is_one bytes)."""
         g1, n = _arr(g1, G1_BYTES)
@@ -167,8 +207,8 @@ class Engine:
         else:
             assert pairs_per_check > 0 and n % pairs_per_check == 0
             n_checks = n // pairs_per_check
-        out = np.empty(n_checks * GT_BYTES, dtype=np.uint8)
-        is_one = np.empty(n_checks, dtype=np.uint8)
+        out = _out(out, n_checks * GT_BYTES)
+        is_one = _out(is_one, n_checks)
         self._check(self.lib.bn254_pairing_product_many(self.ctx, _p(g1), _p(g2), ctypes.c_size_t(pairs_per_check),
                                                         ctypes.c_size_t(n_checks), _p(out), _p(is_one)))
         return out, is_one
@@ -244,20 +284,37 @@ class Engine:
         self._check(self.lib.bn254_gt_eq_many(self.ctx, _p(a), _p(b), _p(eq), ctypes.c_size_t(n)))
         return eq
 
-    def g1_mul(self, g1, fr):
+    def g1_mul(self, g1, fr, out=None):
         g1, n = _arr(g1, G1_BYTES)
         fr, n2 = _arr(fr, FR_BYTES)
         assert n == n2
-        out = np.empty(n * G1_BYTES, dtype=np.uint8)
+        out = _out(out, n * G1_BYTES)
         self._check(self.lib.bn254_g1_mul_many(self.ctx, _p(g1), _p(fr), _p(out), ctypes.c_size_t(n)))
         return out
 
-    def g2_mul(self, g2, fr):
+    def g2_mul(self, g2, fr, out=None):
         g2, n = _arr(g2, G2_BYTES)
         fr, n2 = _arr(fr, FR_BYTES)
         assert n == n2
-        out = np.empty(n * G2_BYTES, dtype=np.uint8)
+        out = _out(out, n * G2_BYTES)
         self._check(self.lib.bn254_g2_mul_many(self.ctx, _p(g2), _p(fr), _p(out), ctypes.c_size_t(n)))
+        return out
+
+    def g1_mul_normalized(self, g1, fr, out=None):
+        """(p * k).normalize() in one call (signed-window kernel; bytes of the reference's normalised result)."""
+        g1, n = _arr(g1, G1_BYTES)
+        fr, n2 = _arr(fr, FR_BYTES)
+        assert n == n2
+        out = _out(out, n * G1_BYTES)
+        self._check(self.lib.bn254_g1_mul_normalized_many(self.ctx, _p(g1), _p(fr), _p(out), ctypes.c_size_t(n)))
+        return out
+
+    def g2_mul_normalized(self, g2, fr, out=None):
+        g2, n = _arr(g2, G2_BYTES)
+        fr, n2 = _arr(fr, FR_BYTES)
+        assert n == n2
+        out = _out(out, n * G2_BYTES)
+        self._check(self.lib.bn254_g2_mul_normalized_many(self.ctx, _p(g2), _p(fr), _p(out), ctypes.c_size_t(n)))
         return out
 
     def g1_normalize(self, g1):
@@ -311,7 +368,7 @@ class Engine:
         self._check(self.lib.bn254_g2_precompute(self.ctx, _p(g2), ctypes.c_size_t(n), ctypes.byref(h)))
         return G2Precomp(self, h)
 
-    def pairing_batch_precomp(self, precomp, g1_shared, g1_var, g2_var, v):
+    def pairing_batch_precomp(self, precomp, g1_shared, g1_var, g2_var, v, out=None, is_one=None):
         """Groth16-shaped checks: per check len(precomp) shared-table pairs + v variable pairs."""
         m = len(precomp) if precomp is not None else 0
         g1_var, nv = _arr(g1_var, G1_BYTES)
@@ -320,8 +377,8 @@ class Engine:
         assert nv == nv2
         n_checks = ns // m if m else nv // v
         assert ns == n_checks * m and nv == n_checks * v
-        out = np.empty(n_checks * GT_BYTES, dtype=np.uint8)
-        is_one = np.empty(n_checks, dtype=np.uint8)
+        out = _out(out, n_checks * GT_BYTES)
+        is_one = _out(is_one, n_checks)
         self._check(self.lib.bn254_pairing_product_precomp_many(
             self.ctx, precomp.handle if precomp is not None else None, _p(g1_shared), _p(g1_var), _p(g2_var),
             ctypes.c_size_t(v), ctypes.c_size_t(n_checks), _p(out), _p(is_one)))
@@ -349,6 +406,26 @@ class Engine:
     def g2_mul_dev(self, d_g2, d_fr, d_out, n):
         self._check(self.lib.bn254_g2_mul_many_dev(self.ctx, ctypes.c_void_p(d_g2), ctypes.c_void_p(d_fr),
                                                    ctypes.c_void_p(d_out), ctypes.c_size_t(n)))
+
+    def g1_mul_normalized_dev(self, d_g1, d_fr, d_out, n):
+        self._check(self.lib.bn254_g1_mul_normalized_many_dev(self.ctx, ctypes.c_void_p(d_g1), ctypes.c_void_p(d_fr),
+                                                              ctypes.c_void_p(d_out), ctypes.c_size_t(n)))
+
+    def g2_mul_normalized_dev(self, d_g2, d_fr, d_out, n):
+        self._check(self.lib.bn254_g2_mul_normalized_many_dev(self.ctx, ctypes.c_void_p(d_g2), ctypes.c_void_p(d_fr),
+                                                              ctypes.c_void_p(d_out), ctypes.c_size_t(n)))
+
+    def miller_product_dev(self, d_g1, d_g2, n, d_out):
+        """Un-exponentiated product of n device-resident pairs into d_out (384 B); asynchronous."""
+        self._check(self.lib.bn254_miller_product_dev(self.ctx, ctypes.c_void_p(d_g1), ctypes.c_void_p(d_g2), ctypes.c_size_t(n),
+                                                      ctypes.c_void_p(d_out)))
+
+    def pairing_timed_dev(self, d_g1, d_g2, d_out, n):
+        """bn254_pairing_many_dev_timed: per-kernel milliseconds [affine, lines, miller, easy, hard]."""
+        ms = (ctypes.c_float * 5)()
+        self._check(self.lib.bn254_pairing_many_dev_timed(self.ctx, ctypes.c_void_p(d_g1), ctypes.c_void_p(d_g2), ctypes.c_void_p(d_out),
+                                                          ctypes.c_size_t(n), ms))
+        return [float(x) for x in ms]
 
     def g1_from_compressed_dev(self, d_enc, d_out, d_status, n):
         self._check(self.lib.bn254_g1_from_compressed_many_dev(self.ctx, ctypes.c_void_p(d_enc), ctypes.c_void_p(d_out),
@@ -382,16 +459,41 @@ class Engine:
         return ms.value, ops.value
 
 
-def pairing_product_sharded(engines, g1, g2):
+def _ctx_list(engines):
+    return (ctypes.c_void_p * len(engines))(*[e.ctx.value if isinstance(e.ctx, ctypes.c_void_p) else e.ctx for e in engines])
+
+
+def pairing_product_sharded(engines, g1, g2, timed=False):
     """One product over all pairs, sharded by index range over several engines (one per GPU);
-    384-byte partials gathered to engines[0] by peer copy, one final exponentiation."""
+    384-byte partials gathered to engines[0] by peer copy, one final exponentiation.
+    timed=True also returns [miller_ms, gather_ms, combine_ms] (host clock, extra synchronisations)."""
     g1, n = _arr(g1, G1_BYTES)
     g2, n2 = _arr(g2, G2_BYTES)
     assert n == n2 and engines
     lib = engines[0].lib
-    ctxs = (ctypes.c_void_p * len(engines))(*[e.ctx for e in engines])
+    ctxs = _ctx_list(engines)
     out = np.empty(GT_BYTES, dtype=np.uint8)
     is_one = np.empty(1, dtype=np.uint8)
+    if timed:
+        ms = (ctypes.c_double * 3)()
+        engines[0]._check(lib.bn254_pairing_product_sharded_timed(ctxs, ctypes.c_size_t(len(engines)), _p(g1), _p(g2),
+                                                                  ctypes.c_size_t(n), _p(out), _p(is_one), ms))
+        return out, bool(is_one[0]), [float(x) for x in ms]
     engines[0]._check(lib.bn254_pairing_product_sharded(ctxs, ctypes.c_size_t(len(engines)), _p(g1), _p(g2),
                                                         ctypes.c_size_t(n), _p(out), _p(is_one)))
     return out, bool(is_one[0])
+
+
+def pairing_sharded(engines, g1, g2, out=None):
+    """n independent pairings in ONE call over a device list (bn254_pairing_many_sharded): contiguous index ranges,
+    one host thread per engine, results written to the caller's index ranges."""
+    g1, n = _arr(g1, G1_BYTES)
+    g2, n2 = _arr(g2, G2_BYTES)
+    assert n == n2 and engines
+    if out is None:
+        out = np.empty(n * GT_BYTES, dtype=np.uint8)
+    else:
+        assert out.dtype == np.uint8 and out.size == n * GT_BYTES and out.flags["C_CONTIGUOUS"]
+    engines[0]._check(engines[0].lib.bn254_pairing_many_sharded(_ctx_list(engines), ctypes.c_size_t(len(engines)), _p(g1), _p(g2),
+                                                                _p(out), ctypes.c_size_t(n)))
+    return out

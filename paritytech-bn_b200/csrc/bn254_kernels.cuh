@@ -149,9 +149,31 @@ __global__ void __launch_bounds__(BN_SYNC_MAX_BLOCK, 1) k_final_exp_hard_sync(co
     bool s = live && some_in[i] != 0;
     Fq12 f, r;
     if (s) f = in[i]; else f = fq12_zero();
-    s_fq12_final_exp_last_chunk<true>(r, f, s_base());
+    const sp base = s_base();
+    s_fq12_final_exp_last_chunk<true>(r, f, base);
+    // Results leave through the slot file: every thread parks its 384 bytes in its own slots, then each warp stores its 32
+    // consecutive records (12 KB, contiguous in the AoS output) as 24 fully coalesced 512-byte rows.  A per-thread store is
+    // 16 bytes at a 384-byte stride per lane -- half-filled sectors in HBM and, for a pinned (zero-copy) output buffer,
+    // 16-byte PCIe writes.
+    if (out) {
+        if (!s) r = fq12_zero();
+        const uint4* rw = reinterpret_cast<const uint4*>(&r);
+#pragma unroll
+        for (int w = 0; w < 24; w++) sts128(base + 16 * w, rw[w]);
+        __syncwarp();
+        const unsigned stride = blockDim.x > BN_SLOT_BLOCK7 ? BN_SLOT_STRIDE6 : BN_SLOT_STRIDE;
+        const unsigned lane = threadIdx.x & 31u;
+        const sp wbase = base - lane * stride;                       // slots of lane 0 of this warp
+        const size_t first = i - lane;                               // record index of lane 0
+        uint4* o = reinterpret_cast<uint4*>(out + first);
+#pragma unroll 4
+        for (int row = 0; row < 24; row++) {
+            unsigned g = row * 32u + lane;                           // 16-byte word of the warp's 12 KB
+            unsigned t = g / 24u, w = g - t * 24u;
+            if (first + t < n) o[g] = lds128(wbase + t * stride + 16 * w);
+        }
+    }
     if (!live) return;
-    if (out) out[i] = r;
     if (some) some[i] = s ? 1 : 0;
     if (is_one) {
         Fq12 one = fq12_one();
@@ -486,6 +508,17 @@ __global__ void __launch_bounds__(BN_BLOCK, BN_MIN_BLOCKS_MTAB) k_miller_table_a
     if (ok_out) ok_out[i] = good ? 1 : 0;
 }
 
+// out[i] = Fq12::one() (the empty product, src/groups/mod.rs:610, :922-924)
+BN_KERNEL k_fq12_set_one(Fq12* __restrict__ out, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    out[i] = fq12_one();
+}
+// flag[0] = 1 if any of the n status bytes is zero (miller_loop_batch: a point at infinity anywhere -> Err, src/lib.rs:629-630)
+__global__ void k_any_zero_flag(const uint8_t* __restrict__ ok, int* __restrict__ flag, size_t n) {
+    size_t i = gtid();
+    if (i < n && ok[i] == 0) atomicExch(flag, 1);
+}
 // out[g] = prod_{j < group} in[g*group + j]
 BN_KERNEL k_fq12_group_product(const Fq12* __restrict__ in, size_t group, Fq12* __restrict__ out, size_t n_groups) {
     size_t g = gtid();
@@ -554,6 +587,18 @@ BN_KERNEL k_jac_mul(const Jac<F>* __restrict__ p, const Fq* __restrict__ fr, Jac
     uint32_t k[8];
     fr_to_canonical(k, m.v);
     jac_mul(r, x, k);
+    out[i] = r;
+}
+// (p * k).normalize() by the signed 4-bit window (jac_mul_normalized, bn_curve.cuh); the 8-entry table lives in local memory
+template <class F>
+BN_KERNEL k_jac_mul_window(const Jac<F>* __restrict__ p, const Fq* __restrict__ fr, Jac<F>* __restrict__ out, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Jac<F> x = p[i], r;
+    Fq m = fr[i];
+    uint32_t k[8];
+    fr_to_canonical(k, m.v);
+    jac_mul_normalized(r, x, k);
     out[i] = r;
 }
 template <class F>

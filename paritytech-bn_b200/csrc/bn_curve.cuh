@@ -123,6 +123,67 @@ template <class F> BN_HD void jac_normalize(Jac<F>& r, const Jac<F>& p) {
     if (jac_to_affine(a, p)) { r.x = a.x; r.y = a.y; r.z = F::one(); } else { r = p; }
 }
 
+// Signed 4-bit window recoding of a canonical scalar k < 2^255: k = sum_i d_i 16^i with d_i in {-7..8}.
+// mag holds |d_i| as nibble i (0..8), sgn bit i is set where d_i < 0.  (k < r < 2^254, so the top digit is at most 4.)
+BN_HD void wnaf4_fixed_recode(uint32_t (&mag)[8], uint32_t (&sgn)[2], const uint32_t (&k)[8]) {
+    uint32_t carry = 0;
+    sgn[0] = sgn[1] = 0;
+    for (int w = 0; w < 8; w++) {
+        uint32_t m = 0;
+        for (int j = 0; j < 8; j++) {
+            uint32_t d = ((k[w] >> (4 * j)) & 15u) + carry;     // 0..16
+            carry = d > 8u ? 1u : 0u;
+            uint32_t neg = carry;
+            uint32_t a = neg ? 16u - d : d;                      // 0..8
+            m |= a << (4 * j);
+            int i = w * 8 + j;
+            sgn[i >> 5] |= neg << (i & 31);
+        }
+        mag[w] = m;
+    }
+}
+// k * P for callers that normalise the result: fixed signed 4-bit window over the canonical scalar -- a table of
+// 1P..8P (4 doublings + 3 additions), then 63 x (4 doublings + one table addition with a conditional negation).
+// Every lane of a warp runs the same sequence (the bit-serial ladder of jac_mul executes the addition for almost
+// every bit once 32 lanes are combined).  The Jacobian representative differs from jac_mul's; the group element
+// is the same (the a = 0 formulas never use b, so this holds for any input the reference computes on), hence the
+// normalised bytes agree.  Returns with z = 0 when the result is the point at infinity.
+template <class F> BN_HD void jac_mul_window(Jac<F>& r, const Jac<F>& p, const uint32_t (&k)[8]) {
+    Jac<F> tab[8];
+    tab[0] = p;
+    jac_double(tab[1], p);
+    jac_add(tab[2], tab[1], p);
+    jac_double(tab[3], tab[1]);
+    jac_add(tab[4], tab[3], p);
+    jac_double(tab[5], tab[2]);
+    jac_add(tab[6], tab[5], p);
+    jac_double(tab[7], tab[3]);
+    uint32_t mag[8], sgn[2];
+    wnaf4_fixed_recode(mag, sgn, k);
+    Jac<F> acc;
+    jac_set_zero(acc);
+    for (int i = 63; i >= 0; i--) {
+        if (i != 63) { jac_double(acc, acc); jac_double(acc, acc); jac_double(acc, acc); jac_double(acc, acc); }
+        uint32_t a = (mag[i >> 3] >> (4 * (i & 7))) & 15u;
+        if (a != 0) {
+            Jac<F> t = tab[a - 1];
+            if ((sgn[i >> 5] >> (i & 31)) & 1u) F::neg(t.y, t.y);
+            jac_add(acc, acc, t);
+        }
+    }
+    r = acc;
+}
+// (p * k).normalize() with the reference's bytes in every case: a result at infinity (k = 0, p at infinity, or a
+// point whose multiple vanishes) is recomputed by the reference's own ladder, whose (x, y, 0) it leaves untouched.
+template <class F> BN_HD void jac_mul_normalized(Jac<F>& r, const Jac<F>& p, const uint32_t (&k)[8]) {
+    Jac<F> t;
+    jac_mul_window(t, p, k);
+    if (F::is_zero(t.z)) { jac_mul(r, p, k); return; }
+    Aff<F> a;
+    jac_to_affine(a, t);
+    r.x = a.x; r.y = a.y; r.z = F::one();
+}
+
 // Fr: canonical scalar bits from the Montgomery image, U256::from(Fr), src/fields/fp.rs:13-20.
 // One Montgomery reduction mod r of the 256-bit value (k*R) -> k.
 BN_HD void fr_to_canonical(uint32_t (&out)[8], const uint32_t (&m)[8]) {

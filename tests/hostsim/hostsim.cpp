@@ -58,6 +58,23 @@ extern "C" void hs_g1_mul(const void* p, const void* fr, void* o, size_t n) {
 extern "C" void hs_g2_mul(const void* p, const void* fr, void* o, size_t n) {
     for (size_t i = 0; i < n; i++) { G2 x = ld<G2>(p, i), r; Fq m = ld<Fq>(fr, i); uint32_t k[8]; fr_to_canonical(k, m.v); jac_mul(r, x, k); st(o, i, r); }
 }
+// (p * k).normalize() by the signed 4-bit window (k_jac_mul_window's body)
+extern "C" void hs_g1_mul_normalized(const void* p, const void* fr, void* o, size_t n) {
+    for (size_t i = 0; i < n; i++) { G1 x = ld<G1>(p, i), r; Fq m = ld<Fq>(fr, i); uint32_t k[8]; fr_to_canonical(k, m.v); jac_mul_normalized(r, x, k); st(o, i, r); }
+}
+extern "C" void hs_g2_mul_normalized(const void* p, const void* fr, void* o, size_t n) {
+    for (size_t i = 0; i < n; i++) { G2 x = ld<G2>(p, i), r; Fq m = ld<Fq>(fr, i); uint32_t k[8]; fr_to_canonical(k, m.v); jac_mul_normalized(r, x, k); st(o, i, r); }
+}
+// digits of the recoding: out[i] = d_i in -7..8 for i < 64
+extern "C" void hs_wnaf4_fixed_recode(const void* k_le, signed char* out) {
+    uint32_t k[8], mag[8], sgn[2];
+    memcpy(k, k_le, 32);
+    wnaf4_fixed_recode(mag, sgn, k);
+    for (int i = 0; i < 64; i++) {
+        int a = (mag[i >> 3] >> (4 * (i & 7))) & 15;
+        out[i] = (signed char)(((sgn[i >> 5] >> (i & 31)) & 1) ? -a : a);
+    }
+}
 extern "C" void hs_fr_to_canonical(const void* fr, void* o, size_t n) {
     for (size_t i = 0; i < n; i++) { Fq m = ld<Fq>(fr, i), r; fr_to_canonical(r.v, m.v); st(o, i, r); }
 }

@@ -199,6 +199,48 @@ def test_scalar_mul_vs_oracle(eng):
     assert eng.g1_normalize(inf).tobytes() == inf.tobytes()
 
 
+def test_scalar_mul_normalized_vs_oracle(eng):
+    """bn254_g{1,2}_mul_normalized_many (signed-window kernel) == the oracle's (p * k).normalize(): edge scalars, extreme
+    window digits, z == 1 bases and points at infinity next to random inputs."""
+    n = 2048
+    ks = util.scalars(n, stream=13)
+    base1, base2 = _workload(n, 14)
+    R = o.R_ORDER
+    sc = [0, 1, 2, R - 1, 8, 9, 16, int("9" * 60, 16) % R, int("f" * 63, 16) % R, int("8" * 63, 16) % R, R - 2] + ks[11:]
+    fr = util.fr_bytes(sc)
+    base1 = base1.reshape(n, G1).copy(); base2 = base2.reshape(n, G2).copy()
+    base1[20], base2[20] = util.G1_GEN, util.G2_GEN
+    base1[21], base2[21] = util.G1_INF, util.G2_INF
+    base1, base2 = base1.reshape(-1), base2.reshape(-1)
+    assert eng.g1_mul_normalized(base1, fr).tobytes() == c.g1_normalize(c.g1_mul(base1, fr)).tobytes()
+    n2 = 512
+    assert eng.g2_mul_normalized(base2[:n2 * G2], fr[:n2 * FR]).tobytes() == c.g2_normalize(c.g2_mul(base2[:n2 * G2], fr[:n2 * FR])).tobytes()
+
+
+@pytest.mark.parametrize("which,log2n", [("g1", 20), ("g2", 18)], ids=["g1_mul_n=2^20", "g2_mul_n=2^18"])
+def test_scalar_mul_config4_sizes(eng, which, log2n):
+    """BASELINE config #4 at its own sizes (2^20 G1 * Fr, 2^18 G2 * Fr).  Bases k_i * G with z != 1 and Montgomery scalars incl.
+    0, 1, 2, r-1.  Normalised bytes of the window kernel against the oracle on a 2^16 sample, raw Jacobian bytes of the
+    reference-sequence kernel on 2^14, and over ALL elements the two kernels must agree after normalisation."""
+    n = 1 << log2n
+    unit = G1 if which == "g1" else G2
+    gen = util.G1_GEN if which == "g1" else util.G2_GEN
+    mul, mul_n, norm = (eng.g1_mul, eng.g1_mul_normalized, eng.g1_normalize) if which == "g1" else (eng.g2_mul, eng.g2_mul_normalized, eng.g2_normalize)
+    cmul, cnorm = (c.g1_mul, c.g1_normalize) if which == "g1" else (c.g2_mul, c.g2_normalize)
+    base = mul(np.tile(gen, n), util.fr_images(n, stream=91))                        # k_i * G, Jacobian with z != 1
+    fr = util.fr_images(n, stream=92)
+    fr[:4 * FR] = util.fr_bytes([0, 1, 2, o.R_ORDER - 1])
+    raw = mul(base, fr)
+    nrm = mul_n(base, fr)
+    assert norm(raw).tobytes() == nrm.tobytes()                                      # all n elements, both kernels
+    m = 1 << 16
+    idx = np.concatenate([np.arange(0, 64), np.arange(64, n, max(1, (n - 64) // (m - 64)))[:m - 64]])
+    bs, fs = base.reshape(n, unit)[idx].reshape(-1), fr.reshape(n, FR)[idx].reshape(-1)
+    assert nrm.reshape(n, unit)[idx].tobytes() == cnorm(cmul(bs, fs)).tobytes()
+    m2 = 1 << 14
+    assert raw[:m2 * unit].tobytes() == cmul(base[:m2 * unit], fr[:m2 * FR]).tobytes()  # the reference's own Jacobian representative
+
+
 def test_gt_algebra_and_joux(eng):
     """Gt::{mul,pow,inverse,==} and the Joux three-party check of examples/joux.rs:7-21."""
     a, b, cc = util.scalars(3, stream=21)
@@ -222,10 +264,12 @@ def test_gt_algebra_and_joux(eng):
     assert some[0] == 0
 
 
-def test_full_size_products_known_answer(eng):
-    """2^16 Groth16-shaped checks (BASELINE config #3 size) through a size-independent property:
-    valid checks are exactly one, tampered ones are not; inputs made by the CUDA scalar-mul kernels."""
-    n_checks = int(os.environ.get("BN_TEST_FULL_CHECKS", str(1 << 14)))
+@pytest.mark.parametrize("log2n", [16], ids=["n_checks=2^16"])
+def test_full_size_products_known_answer(eng, log2n):
+    """2^16 Groth16-shaped checks (BASELINE config #3 size): valid checks are exactly one, tampered ones are not, and ALL
+    Gt values + accept bytes equal the oracle's pairing_batch -- flat 4-pair layout and the shared-G2Precomp entry point.
+    Inputs made by the CUDA scalar-mul kernels."""
+    n_checks = int(os.environ.get("BN_TEST_FULL_CHECKS", str(1 << log2n)))
 
     def smul(which, ks):
         fr = util.fr_bytes(ks)
@@ -238,11 +282,12 @@ def test_full_size_products_known_answer(eng):
     assert (is_one == w["valid"]).all()
     ones = out.reshape(n_checks, GT)[w["valid"] == 1]
     assert (ones == util.GT_ONE).all()
-    # spot-check 64 of them bit-for-bit against the oracle
-    idx = np.arange(0, n_checks, max(1, n_checks // 64))[:64]
-    g1s = w["g1"].reshape(n_checks, 4 * G1)[idx].reshape(-1)
-    g2s = w["g2"].reshape(n_checks, 4 * G2)[idx].reshape(-1)
-    assert out.reshape(n_checks, GT)[idx].tobytes() == c.pairing_product_many(g1s, g2s, 4)[0].tobytes()
+    rout, ris = c.pairing_product_many(w["g1"], w["g2"], 4)
+    assert out.tobytes() == rout.tobytes() and (ris == is_one).all()
+    pc = eng.g2_precompute(w["vk_g2"])
+    out2, is_one2 = eng.pairing_batch_precomp(pc, w["g1_shared"], w["g1_var"], w["g2_var"], 1)
+    pc.close()
+    assert out2.tobytes() == rout.tobytes() and (is_one2 == is_one).all()
 
 
 def test_sharded_product(eng):
@@ -269,6 +314,89 @@ def test_sharded_product(eng):
     assert not is_one and out.tobytes() == c.pairing_batch(g1, g2).tobytes()
     for e in engines[1:]:
         e.close()
+
+
+def _engines_for_sharding(eng, want):
+    """`want` engines over the visible devices (round-robin): several contexts share a GPU when there are fewer devices."""
+    import torch
+
+    import paritytech_bn_b200 as bn
+    ndev = torch.cuda.device_count()
+    return [eng] + [bn.Engine(d % ndev) for d in range(1, want)]
+
+
+@pytest.mark.parametrize("log2n", [18], ids=["n_pairs=2^18"])
+def test_sharded_product_known_answer_large(eng, log2n):
+    """BASELINE config #5's exchange step at size: ONE product of 2^18 pairs split over 4 contexts (4 GPUs when the box has
+    them, otherwise contexts sharing devices), 384-byte partials gathered by peer copy, one final exponentiation.
+    sum a_i b_i == 0 mod r makes the product exactly one -- no 2^18-pairing CPU run needed; one tampered pair
+    must flip the answer; 1-, 2- and 4-way splits give identical bytes; points from the CUDA scalar-mul kernels."""
+    import paritytech_bn_b200 as bn
+    n = 1 << log2n
+    ks1 = util.scalars(n, stream=43)
+    ks2 = util.scalars(n, stream=44)
+    tot = sum(x * y for x, y in zip(ks1[:-1], ks2[:-1])) % o.R_ORDER
+    ks1[-1] = (-tot * pow(ks2[-1], -1, o.R_ORDER)) % o.R_ORDER
+    g1 = eng.g1_mul(np.tile(util.G1_GEN, n), util.fr_bytes(ks1))
+    g2 = eng.g2_mul(np.tile(util.G2_GEN, n), util.fr_bytes(ks2))
+    engines = _engines_for_sharding(eng, 4)
+    try:
+        out4, one4, ms = bn.pairing_product_sharded(engines, g1, g2, timed=True)
+        assert one4 and out4.tobytes() == util.GT_ONE.tobytes()
+        assert len(ms) == 3 and all(x >= 0 for x in ms)
+        out2, one2 = bn.pairing_product_sharded(engines[:2], g1, g2)
+        out1, one1 = bn.pairing_product_sharded(engines[:1], g1, g2)
+        assert one2 and one1 and out2.tobytes() == out1.tobytes() == out4.tobytes()
+        g1[:G1] = util.G1_GEN                                   # tamper with one pair
+        t4, tone4 = bn.pairing_product_sharded(engines, g1, g2)
+        t1, tone1 = bn.pairing_product_sharded(engines[:1], g1, g2)
+        assert not tone4 and not tone1 and t4.tobytes() == t1.tobytes() != util.GT_ONE.tobytes()
+        # every partial is an arbitrary Fq12: the per-context Miller products are not one on their own
+        lo, hi = bn.shard_range(n, 1, 4)
+        assert eng.miller_product(g1[lo * G1:hi * G1], g2[lo * G2:hi * G2]).tobytes() != util.GT_ONE.tobytes()
+    finally:
+        for e in engines[1:]:
+            e.close()
+
+
+@pytest.mark.parametrize("n,ways", [(1, 2), (7, 3), (1000, 2), (70001, 4)])
+def test_pairing_many_sharded(eng, n, ways):
+    """bn254_pairing_many_sharded: ONE call, n independent pairs over a context list -- every result lands in the caller's
+    own index range and equals the single-context call (and the oracle on a sample), ragged splits and n < ways included."""
+    import paritytech_bn_b200 as bn
+    base = min(n, 1024)
+    p1, p2 = util.points_cpu(util.scalars(base, stream=45), util.scalars(base, stream=46))
+    idx = (np.arange(n) * 2654435761 % base).astype(np.int64)
+    g1 = p1.reshape(base, G1)[idx].copy(); g2 = p2.reshape(base, G2)[(idx * 5 + 1) % base].copy()
+    if n > 10:
+        g1[n // 2] = util.G1_INF
+    g1, g2 = g1.reshape(-1), g2.reshape(-1)
+    engines = _engines_for_sharding(eng, ways)
+    try:
+        got = bn.pairing_sharded(engines, g1, g2)
+    finally:
+        for e in engines[1:]:
+            e.close()
+    assert got.tobytes() == eng.pairing(g1, g2).tobytes()
+    m = min(n, 64)
+    sel = np.unique(np.concatenate([np.arange(m), np.arange(n - m, n), [n // 2]]))
+    exp = c.pairing_many(g1.reshape(n, G1)[sel].reshape(-1), g2.reshape(n, G2)[sel].reshape(-1))
+    assert got.reshape(n, GT)[sel].tobytes() == exp.tobytes()
+
+
+def test_abi_smoke_compiled_c_consumer():
+    """tests/abi/abi_smoke.c, built with gcc against include/bn254_b200.h + libbn254_b200.so alone: struct sizes, argument
+    order and NULL-able outputs as a C (or bindgen) user meets them; it runs the reference's test_reduced_pairing vector
+    and a 4-pair product."""
+    import subprocess
+
+    from tests import abi
+    exe = abi.build()
+    import paritytech_bn_b200 as bn
+    env = dict(os.environ, LD_LIBRARY_PATH=os.path.dirname(bn.library_path()) + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
+    p = subprocess.run([exe], capture_output=True, text=True, timeout=600, env=env)
+    assert p.returncode == 0, p.stdout + p.stderr
+    assert "abi_smoke ok" in p.stdout
 
 
 def test_conditional_subtraction_tie_cases(eng):
@@ -336,11 +464,7 @@ def test_fused_and_split_miller_paths_agree(eng):
     exp, exp_ok = c.miller_loop_many(g2, g1)
     got, ok = eng.miller_loop_many(g2, g1)
     assert got.tobytes() == exp.tobytes() and (ok == exp_ok).all()
-    os.environ["BN254_FUSED_MILLER"] = "1"
-    try:
-        e2 = bn.Engine(0)
-    finally:
-        del os.environ["BN254_FUSED_MILLER"]
+    e2 = bn.Engine(0, fused_miller=1)
     got2, ok2 = e2.miller_loop_many(g2, g1)
     e2.close()
     assert got2.tobytes() == exp.tobytes() and (ok2 == exp_ok).all()
@@ -365,10 +489,11 @@ def test_miller_product_and_distributed_protocol_single_process(eng):
     assert out1.tobytes() == out.tobytes()
 
 
-def test_pairing_full_batch_round_trip_properties(eng):
-    """2^16 pairings (BASELINE config #2 size) through size-independent properties: bilinearity in the first
-    argument e(2P, Q) == e(P, Q)^2 for every pair, no result equals one, and a 256-element sample bit-exact."""
-    n = int(os.environ.get("BN_TEST_FULL_PAIRINGS", str(1 << 16)))
+@pytest.mark.parametrize("log2n", [16], ids=["n=2^16"])
+def test_pairing_full_batch_round_trip_properties(eng, log2n):
+    """2^16 pairings (BASELINE config #2 size): ALL outputs byte-compared with the oracle, plus the
+    size-independent properties -- bilinearity in the first argument e(2P, Q) == e(P, Q)^2 for every pair, no result one."""
+    n = int(os.environ.get("BN_TEST_FULL_PAIRINGS", str(1 << log2n)))
     fr1, fr2 = util.fr_bytes(util.scalars(n, stream=81)), util.fr_bytes(util.scalars(n, stream=82))
     g1 = eng.g1_mul(np.tile(util.G1_GEN, n), fr1)
     g2 = eng.g2_mul(np.tile(util.G2_GEN, n), fr2)
@@ -378,9 +503,7 @@ def test_pairing_full_batch_round_trip_properties(eng):
     e2 = eng.pairing(g1x2, g2)
     assert e2.tobytes() == eng.gt_mul(e1, e1).tobytes()
     assert not (e1.reshape(n, GT) == util.GT_ONE).all(axis=1).any()
-    idx = np.arange(0, n, max(1, n // 256))[:256]
-    s1 = g1.reshape(n, G1)[idx].reshape(-1); s2 = g2.reshape(n, G2)[idx].reshape(-1)
-    assert e1.reshape(n, GT)[idx].tobytes() == c.pairing_many(s1, s2).tobytes()
+    assert e1.tobytes() == c.pairing_many(g1, g2).tobytes()
 
 
 def test_pairing_across_table_chunk_boundary(eng):
@@ -422,19 +545,60 @@ def test_slot_file_and_local_memory_paths_agree(eng, n):
     exp_f, exp_ok = c.miller_loop_many(g2[:m * G2], g1[:m * G1])
     ref = eng.pairing(g1, g2)
     assert ref[:m * GT].tobytes() == exp.tobytes()
-    for env in ({"BN254_FEXP_SMEM": "0", "BN254_MILLER_SMEM": "0", "BN254_LINES_SMEM": "0"}, {"BN254_FEXP_SMEM": "1"}, {"BN254_FEXP_SMEM": "2", "BN254_MILLER_SMEM": "1"},
-                {"BN254_BIG_BLOCKS": "2"}):   # 512-thread blocks on 6 slots per thread (otherwise chosen from 2^19 pairings up)
-        os.environ.update(env)
-        try:
-            e2 = bn.Engine(0)
-        finally:
-            for k in env:
-                del os.environ[k]
+    for opt in (dict(fexp_smem=0, miller_smem=0, lines_smem=0), dict(fexp_smem=1), dict(fexp_smem=2, miller_smem=1),
+                dict(big_blocks=2)):    # 512-thread blocks on 6 slots per thread (otherwise chosen from 2^19 pairings up)
+        e2 = bn.Engine(0, coop_max_n=0, **opt)
         got = e2.pairing(g1, g2)
         f, ok = e2.miller_loop_many(g2, g1)
         e2.close()
-        assert got.tobytes() == ref.tobytes(), env
-        assert f[:m * GT].tobytes() == exp_f.tobytes() and (ok[:m] == exp_ok).all(), env
+        assert got.tobytes() == ref.tobytes(), opt
+        assert f[:m * GT].tobytes() == exp_f.tobytes() and (ok[:m] == exp_ok).all(), opt
+
+
+def test_environment_switches_still_fill_the_defaults(eng):
+    """The BN254_* variables are only the default filler of bn254_ctx_options: an engine created under BN254_FEXP_SMEM=0
+    takes the local-memory final exponentiation and still produces the same bytes."""
+    import paritytech_bn_b200 as bn
+    g1, g2 = util.points_cpu(util.scalars(70, stream=73), util.scalars(70, stream=74))
+    os.environ["BN254_FEXP_SMEM"] = "0"
+    try:
+        e2 = bn.Engine(0)
+    finally:
+        del os.environ["BN254_FEXP_SMEM"]
+    got = e2.pairing(g1, g2)
+    e2.close()
+    assert got.tobytes() == eng.pairing(g1, g2).tobytes() == c.pairing_many(g1, g2).tobytes()
+
+
+@pytest.mark.parametrize("v", [1, 4, 8])
+def test_product_checks_on_512_thread_blocks(eng, v):
+    """k_miller_product_sync on 6 slots per thread (512-thread blocks, big_blocks=2): pairing_batch with v pairs per check and
+    pairing_batch_precomp with shared tables, byte-for-byte against the oracle (a 7th-slot access would corrupt a neighbour)."""
+    import paritytech_bn_b200 as bn
+    n_checks = 1200                                    # > 512, so that sync_block picks 512
+    base = 256
+    p1, p2 = util.points_cpu(util.scalars(base, stream=75), util.scalars(base, stream=76))
+    idx = (np.arange(n_checks * v) * 2654435761 % base).astype(np.int64)
+    g1 = p1.reshape(base, G1)[idx].copy(); g2 = p2.reshape(base, G2)[(idx * 3 + 1) % base].copy()
+    g1[5] = util.G1_INF
+    g1, g2 = g1.reshape(-1), g2.reshape(-1)
+    e2 = bn.Engine(0, big_blocks=2)
+    try:
+        out, is_one = e2.pairing_batch(g1, g2, pairs_per_check=v)
+        rout, ris = c.pairing_product_many(g1, g2, v)
+        assert out.tobytes() == rout.tobytes() and (is_one == ris).all()
+        if v <= 4:
+            vk = p2[:3 * G2]
+            pc = e2.g2_precompute(vk)
+            g1s = p1.reshape(base, G1)[(np.arange(n_checks * 3) * 7 + 2) % base].reshape(-1)
+            out2, _ = e2.pairing_batch_precomp(pc, g1s, g1, g2, v)
+            pc.close()
+            # oracle: the same check as one flat product of 3 + v pairs
+            f1 = np.concatenate([g1s.reshape(n_checks, 3 * G1), g1.reshape(n_checks, v * G1)], axis=1).reshape(-1)
+            f2 = np.concatenate([np.tile(vk, (n_checks, 1)), g2.reshape(n_checks, v * G2)], axis=1).reshape(-1)
+            assert out2.tobytes() == c.pairing_product_many(f1, f2, 3 + v)[0].tobytes()
+    finally:
+        e2.close()
 
 
 @pytest.mark.parametrize("name,unit,ref", [

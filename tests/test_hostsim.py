@@ -140,6 +140,38 @@ def test_groups_and_scalar_mul():
     assert out.tobytes() == c.g2_mul(q, fr).tobytes()
 
 
+def test_window_scalar_mul_normalized_host_build():
+    """jac_mul_normalized (signed 4-bit window, the body of k_jac_mul_window) == the oracle's (p * k).normalize(), bytes and
+    all: random scalars, the edge scalars 0 / 1 / 2 / r-1, scalars made of extreme digits (8s, 9s -> -7 with carries, 0xf...),
+    the generator with z == 1, and the point at infinity (reference ladder's own (x, y, 0) representative)."""
+    p, q = _points(5)
+    n0 = p.size // G1
+    R = o.R_ORDER
+    ks = [0, 1, 2, R - 1, 8, 9, 16, 0x88888888888888888888888888888888 % R, int("9" * 60, 16) % R, int("f" * 63, 16) % R,
+          int("7" * 63, 16), (1 << 253) + 8, R - 2, R // 2, 0x8000000000000000]
+    ks += [rng.randrange(R) for _ in range(17)]
+    n = len(ks)
+    P = np.tile(p.reshape(n0, G1), (n // n0 + 1, 1))[:n].copy()
+    Q = np.tile(q.reshape(n0, G2), (n // n0 + 1, 1))[:n].copy()
+    P[5] = np.frombuffer(o.to_bytes((1, 2, 1)), dtype=np.uint8)                                 # generator, z == one
+    P[6] = np.frombuffer(o.to_bytes((0, 1, 0)), dtype=np.uint8)                                 # infinity
+    P[7] = np.frombuffer(o.to_bytes((5, 7, 0)), dtype=np.uint8)                                 # infinity, odd representative
+    Q[6] = np.frombuffer(o.to_bytes(((0, 0), (1, 0), (0, 0))), dtype=np.uint8)
+    P, Q = P.reshape(-1), Q.reshape(-1)
+    fr = np.concatenate([np.frombuffer(o.fr_to_bytes(k), dtype=np.uint8) for k in ks]).copy()
+    # the recoding reconstructs the scalar with digits in -7..8
+    for k in ks:
+        d = (ctypes.c_byte * 64)()
+        hostsim.lib().hs_wnaf4_fixed_recode(k.to_bytes(32, "little"), d)
+        assert all(-7 <= x <= 8 for x in d) and sum(int(x) << (4 * i) for i, x in enumerate(d)) == k
+    out = np.empty_like(P)
+    hostsim.lib().hs_g1_mul_normalized(_p(P), _p(fr), _p(out), ctypes.c_size_t(n))
+    assert out.tobytes() == c.g1_normalize(c.g1_mul(P, fr)).tobytes()
+    out = np.empty_like(Q)
+    hostsim.lib().hs_g2_mul_normalized(_p(Q), _p(fr), _p(out), ctypes.c_size_t(n))
+    assert out.tobytes() == c.g2_normalize(c.g2_mul(Q, fr)).tobytes()
+
+
 def test_precompute_miller_pairing(golden):
     p, q = _points(3)
     n = p.size // G1

@@ -40,6 +40,34 @@ def fr_bytes(ks):
     return np.frombuffer(b"".join(((k % R) * MONT % R).to_bytes(32, "little") for k in ks), dtype=np.uint8).copy()
 
 
+def fr_images(n, stream=0):
+    """n random repr(C) Fr images without Python big integers (bench-size inputs): four SplitMix64 words each with the top
+    word cut to 61 bits, so every image is below 2^253 < r.  A uniform image is a uniform scalar (Montgomery scaling is a
+    bijection of Z_r); zero is avoided by setting the lowest bit."""
+    w = splitmix64_stream(SEED + 0x1000003 * stream + 0x5bd1e995, 4 * n).reshape(n, 4).copy()
+    w[:, 3] &= np.uint64((1 << 61) - 1)
+    w[:, 0] |= np.uint64(1)
+    return w.view(np.uint8).reshape(-1).copy()
+
+
+def neg_fr_images(fr):
+    """Images of the negated scalars: r - x limb-wise (numpy multiword borrow arithmetic); x must be in (0, r)."""
+    x = np.ascontiguousarray(fr, dtype=np.uint8).view(np.uint64).reshape(-1, 4)
+    out = np.empty_like(x)
+    borrow = np.zeros(x.shape[0], dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        for j in range(4):
+            rj = np.uint64((R >> (64 * j)) & _M64)
+            t = rj - x[:, j]
+            b1 = (x[:, j] > rj).astype(np.uint64)
+            t2 = t - borrow
+            b2 = (borrow > t).astype(np.uint64)
+            out[:, j] = t2
+            borrow = b1 | b2
+    assert not borrow.any()
+    return out.view(np.uint8).reshape(-1).copy()
+
+
 def fq_mont_bytes(vals):
     return b"".join((v * MONT % Q).to_bytes(32, "little") for v in vals)
 
