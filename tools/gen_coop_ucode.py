@@ -1,0 +1,574 @@
+#!/usr/bin/env python3
+"""Microcode of the warp-cooperative BN254 pairing (latency path, csrc/bn_coop.cuh) -- generator, simulator, emitter.
+
+One WARP computes one pairing.  The warp is a 32-lane vector machine over Fq2: a per-warp file of Fq2 slots in shared memory
+and two instruction kinds, executed in lock step by all lanes, each lane with its own operands:
+
+  MUL  dst = conjA?(sum_{t<na} +-m_t slot[a_t])  *  conjB?(sum_{t<nb} +-m_t slot[b_t])          (one Fq2 product per lane)
+  LIN  dst = half?( P + xi * X ),  P = sum of the terms of group 0, X = sum of the terms of group 1 (xi = 9 + u)
+  INV  dst = (slot[a].c0)^-1 as (Fq, 0)   (one lane, Fermat in registers; everything else is MUL/LIN)
+
+m_t in {1, 2, 3}.  A routine is a short list of steps; a program is a list of calls (routine, base D, base A, base B): operand
+addresses are absolute slots (sel 0) or relative to one of the three bases of the call (sel 1..3), so one MUL12 routine serves
+every Fq12 product of the final exponentiation.  The CUDA side is a generic executor with no knowledge of the algorithm;
+everything algorithmic lives here, where the simulator below runs the very same tables on Python integers against the oracle
+(tests/test_coop_ucode.py), so the schedule is proven on the CPU and the GPU run only has to confirm the executor.
+
+Formulas follow the reference exactly as the throughput kernels do: G2 line steps src/groups/mod.rs:731-776, precompute /
+Miller loop :580-606, :701-728, Fq12 tower src/fields/fq12.rs (mul :316-328, squared :295-303, mul_by_024 :130-196,
+cyclotomic_squared :198-247, final exponentiation :62-110, exp_by_neg_z :121-124 with the width-4 signed window of
+csrc/bn_tower.cuh), fq6 inverse src/fields/fq6.rs:179-191.
+
+usage: gen_coop_ucode.py            write paritytech-bn_b200/csrc/bn_coop_ucode.cuh
+       gen_coop_ucode.py --check    simulate a few pairings against the oracle
+"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+from oracle import bn254_ref as o  # noqa: E402
+
+Q = o.Q
+OP_MUL, OP_LIN, OP_INV = 1, 2, 3
+NT = 8                     # term fields per lane and step (MUL: 4 + 4, LIN: 8)
+NO_DST = 0x3ff             # inactive lane
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# operands
+# ------------------------------------------------------------------------------------------------------------------
+class Ref:
+    """A slot address: absolute (sel 0) or relative to base D (1), A (2), B (3) of the call."""
+    __slots__ = ("sel", "off")
+
+    def __init__(self, sel, off):
+        assert 0 <= sel < 4 and 0 <= off < 256
+        self.sel, self.off = sel, off
+
+    def code(self):
+        return (self.sel << 8) | self.off
+
+    def __add__(self, k):
+        return Ref(self.sel, self.off + k)
+
+    def __repr__(self):
+        return "%s%d" % ("@DAB"[self.sel], self.off)
+
+
+def S(off):
+    return Ref(0, off)
+
+
+D, A, B = Ref(1, 0), Ref(2, 0), Ref(3, 0)
+
+
+def T(ref, sign=1, mult=1, grp=0):
+    """One term: +-mult * slot (group 1 = multiplied by xi in a LIN step)."""
+    assert sign in (1, -1) and mult in (1, 2, 3) and grp in (0, 1)
+    return (ref, sign, mult, grp)
+
+
+def neg(t):
+    return (t[0], -t[1], t[2], t[3])
+
+
+def xi(t):
+    return (t[0], t[1], t[2], 1)
+
+
+def times(t, m):
+    assert t[2] * m <= 3
+    return (t[0], t[1], t[2] * m, t[3])
+
+
+def terms(x):
+    """Normalise: a Ref, a term or a list of either -> list of terms."""
+    if isinstance(x, Ref):
+        return [T(x)]
+    if isinstance(x, tuple) and len(x) == 4 and isinstance(x[0], Ref):
+        return [x]
+    out = []
+    for e in x:
+        out.extend(terms(e))
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# assembler
+# ------------------------------------------------------------------------------------------------------------------
+class Step:
+    def __init__(self, op):
+        self.op, self.lanes = op, []      # lanes: dicts
+
+    def header(self):
+        if self.op == OP_MUL:
+            na = max(len(l["a"]) for l in self.lanes)
+            nb = max(len(l["b"]) for l in self.lanes)
+            return self.op | (na << 4) | (nb << 8)
+        if self.op == OP_LIN:
+            nt = max(len(l["t"]) for l in self.lanes)
+            has_xi = any(t[3] for l in self.lanes for t in l["t"])
+            has_half = any(l["half"] for l in self.lanes)
+            return self.op | (nt << 4) | (int(has_xi) << 12) | (int(has_half) << 13)
+        return self.op
+
+
+class Routine:
+    def __init__(self, name):
+        self.name, self.steps = name, []
+
+    def mul(self, lanes):
+        """lanes: list of (dst, A-side, B-side[, conjA, conjB])."""
+        st = Step(OP_MUL)
+        for ln in lanes:
+            dst, a, b = ln[0], terms(ln[1]), terms(ln[2])
+            ca, cb = (ln[3], ln[4]) if len(ln) > 3 else (False, False)
+            assert 1 <= len(a) <= 4 and 1 <= len(b) <= 4, (self.name, len(a), len(b))
+            assert all(t[3] == 0 for t in a + b), "xi groups exist in LIN steps only"
+            st.lanes.append(dict(dst=dst, a=a, b=b, ca=bool(ca), cb=bool(cb)))
+        self._add(st)
+
+    def lin(self, lanes):
+        """lanes: list of (dst, terms[, half])."""
+        st = Step(OP_LIN)
+        for ln in lanes:
+            dst, t = ln[0], terms(ln[1])
+            assert 1 <= len(t) <= NT, (self.name, len(t))
+            st.lanes.append(dict(dst=dst, t=t, half=bool(ln[2]) if len(ln) > 2 else False))
+        self._add(st)
+
+    def inv(self, dst, src):
+        st = Step(OP_INV)
+        st.lanes.append(dict(dst=dst, t=terms(src)))
+        self._add(st)
+
+    def _add(self, st):
+        assert 1 <= len(st.lanes) <= 32, (self.name, len(st.lanes))
+        # one synchronisation per step: no lane may read a slot that ANOTHER lane of the same step writes
+        # (compared as (sel, off): two different bases may alias only where the call list says so -- checked by the simulator)
+        for i, li in enumerate(st.lanes):
+            srcs = [t[0].code() for k in ("a", "b", "t") for t in li.get(k, [])]
+            for j, lj in enumerate(st.lanes):
+                if i != j:
+                    assert lj["dst"].code() not in srcs, "%s: lane %d reads the destination of lane %d" % (self.name, i, j)
+            for j in range(i):
+                assert st.lanes[j]["dst"].code() != li["dst"].code(), "%s: two lanes write one slot" % self.name
+        self.steps.append(st)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# simulator (Python integers; the semantics the CUDA executor implements)
+# ------------------------------------------------------------------------------------------------------------------
+def _resolve(ref, bases):
+    return ref.off + (0 if ref.sel == 0 else bases[ref.sel - 1])
+
+
+def _sum(slots, tl, bases, grp=None):
+    acc = (0, 0)
+    for ref, sign, mult, g in tl:
+        if grp is not None and g != grp:
+            continue
+        v = slots[_resolve(ref, bases)]
+        v = ((v[0] * mult) % Q, (v[1] * mult) % Q)
+        acc = o.fq2_add(acc, v) if sign > 0 else o.fq2_sub(acc, v)
+    return acc
+
+
+def _conj(v):
+    return (v[0], (-v[1]) % Q)
+
+
+def run_step(slots, st, bases, check_alias=True):
+    writes = {}
+    reads = {}
+    for i, ln in enumerate(st.lanes):
+        for k in ("a", "b", "t"):
+            for t in ln.get(k, []):
+                reads.setdefault(_resolve(t[0], bases), set()).add(i)
+        if st.op == OP_MUL:
+            a = _sum(slots, ln["a"], bases)
+            b = _sum(slots, ln["b"], bases)
+            if ln["ca"]:
+                a = _conj(a)
+            if ln["cb"]:
+                b = _conj(b)
+            r = o.fq2_mul(a, b)
+        elif st.op == OP_LIN:
+            p = _sum(slots, ln["t"], bases, 0)
+            x = _sum(slots, ln["t"], bases, 1)
+            r = o.fq2_add(p, o.fq2_mul_by_nonresidue(x))
+            if ln["half"]:
+                h = pow(2, -1, Q)
+                r = (r[0] * h % Q, r[1] * h % Q)
+        else:
+            v = _sum(slots, ln["t"], bases)
+            r = (pow(v[0], Q - 2, Q), 0)
+        d = _resolve(ln["dst"], bases)
+        assert d not in writes, "two lanes write slot %d" % d
+        writes[d] = (i, r)
+    if check_alias:
+        for d, (i, _) in writes.items():
+            assert reads.get(d, set()) <= {i}, "slot %d written by lane %d is read by lanes %s in the same step" % (d, i, reads[d])
+    for d, (_, r) in writes.items():
+        slots[d] = r
+
+
+def run_program(slots, routines, calls):
+    for rid, bd, ba, bb in calls:
+        for st in routines[rid].steps:
+            run_step(slots, st, (bd, ba, bb))
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# slot map (absolute addresses of the per-warp file; 64 bytes per slot)
+# ------------------------------------------------------------------------------------------------------------------
+ZERO, ONE, C_B3, C_TWQX, C_TWQY = S(0), S(1), S(2), S(3), S(4)
+C_F6C1 = {1: S(5), 2: S(6), 3: S(7)}
+C_F6C2 = {1: S(8), 2: S(9), 3: S(10)}
+C_F12C = {1: S(11), 2: S(12), 3: S(13)}
+N_CONST = 14
+IN_P, IN_Q = S(16), S(19)           # x, y, z each (G1 coordinates embedded as (v, 0))
+PA, QA, QN, Q1, Q2 = S(22), S(24), S(26), S(28), S(30)     # affine points (x, y)
+RX, RY, RZ = S(32), S(33), S(34)    # the running point of the line walk
+L0, LVW, LVV = S(35), S(36), S(37)  # one line: ell_0, ell_vw, ell_vv (field order of src/groups/mod.rs:566-571)
+X2, X4 = S(38), S(39)               # ell_vv * P.x, ell_vw * P.y
+F = S(40)                           # Fq12 accumulator / result, six slots c0.c0, c0.c1, c0.c2, c1.c0, c1.c1, c1.c2
+TMP = S(48)                         # 48 temporaries
+E_BASE, N_EREG = 96, 13             # Fq12 registers of the final exponentiation, six slots each
+N_SLOTS = E_BASE + 6 * N_EREG       # 174
+
+
+def t_(i):
+    assert 0 <= i < 48
+    return TMP + i
+
+
+def ereg(k):
+    assert 0 <= k < N_EREG
+    return E_BASE + 6 * k
+
+
+def fq6_products(dst, xs, ys):
+    """Karatsuba lanes of an Fq6 product (src/fields/fq6.rs:194-208): dst + 0..5 = v0, v1, v2, m01, m12, m02."""
+    xs, ys = [terms(x) for x in xs], [terms(y) for y in ys]
+    return [(dst + 0, xs[0], ys[0]), (dst + 1, xs[1], ys[1]), (dst + 2, xs[2], ys[2]),
+            (dst + 3, xs[0] + xs[1], ys[0] + ys[1]), (dst + 4, xs[1] + xs[2], ys[1] + ys[2]), (dst + 5, xs[0] + xs[2], ys[0] + ys[2])]
+
+
+def fq6_outputs(p):
+    """The three coefficients of the product from the six Karatsuba products at p + 0..5 (as term lists)."""
+    v0, v1, v2, m01, m12, m02 = (T(p + i) for i in range(6))
+    return [[v0, xi(m12), xi(neg(v1)), xi(neg(v2))],
+            [m01, neg(v0), neg(v1), xi(v2)],
+            [m02, neg(v0), neg(v2), v1]]
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# routines
+# ------------------------------------------------------------------------------------------------------------------
+def build_routines():
+    R = {}
+
+    def new(name):
+        r = Routine(name)
+        R[name] = r
+        return r
+
+    # ---- joint affine conversion with ONE inversion (pair_to_affine of csrc/bn254_kernels.cuh; to_affine src/groups/mod.rs:198-217)
+    r = new("TOAFF")
+    px, py, pz = IN_P, IN_P + 1, IN_P + 2
+    qx, qy, qz = IN_Q, IN_Q + 1, IN_Q + 2
+    r.mul([(t_(0), qz, qz, False, True)])                        # norm(q.z)
+    r.mul([(t_(1), pz, t_(0))])
+    r.inv(t_(2), t_(1))
+    r.mul([(t_(3), t_(2), t_(0)), (t_(4), t_(2), pz)])           # 1/p.z, 1/norm
+    r.mul([(t_(5), t_(3), t_(3)), (t_(6), qz, t_(4), True, False)])   # 1/p.z^2, 1/q.z = conj(q.z)/norm
+    r.mul([(PA, px, t_(5)), (t_(7), t_(5), t_(3)), (t_(8), t_(6), t_(6))])
+    r.mul([(PA + 1, py, t_(7)), (QA, qx, t_(8)), (t_(9), t_(8), t_(6))])
+    r.mul([(QA + 1, qy, t_(9))])
+    # line walk starts at R = (Q.x, Q.y, 1); -Q for the NAF digits 3; f = 1
+    r.lin([(RX, QA), (RY, QA + 1), (RZ, ONE), (QN, QA), (QN + 1, T(QA + 1, -1)), (F, ONE)] + [(F + i, ZERO) for i in range(1, 6)])
+
+    # ---- doubling step (src/groups/mod.rs:754-776): R in place, line into L
+    r = new("DBL")
+    r.mul([(t_(0), RX, RY), (t_(1), RX, RX), (t_(2), RY, RY), (t_(3), RZ, RZ), (t_(4), [RY, RZ], [RY, RZ])])
+    r.lin([(t_(5), t_(0), True),                                                   # a = X Y / 2
+           (t_(6), [T(t_(4)), T(t_(2), -1), T(t_(3), -1)]),                        # h = (Y + Z)^2 - b - c
+           (LVW, [T(t_(4), -1), T(t_(2)), T(t_(3))]),                              # ell_vw = -h
+           (LVV, T(t_(1), 1, 3))])                                                 # ell_vv = 3 X^2
+    r.mul([(t_(7), C_B3, t_(3))])                                                  # e = 3 b' Z^2
+    r.lin([(L0, [T(t_(7), 1, 1, 1), T(t_(2), -1, 1, 1)]),                          # ell_0 = xi (e - b)
+           (t_(8), [T(t_(2)), T(t_(7), 1, 3)], True),                              # g = (b + 3 e) / 2
+           (t_(9), [T(t_(2)), T(t_(7), -1, 3)])])                                  # b - f
+    r.mul([(RX, t_(5), t_(9)), (t_(10), t_(8), t_(8)), (t_(11), t_(7), t_(7)), (RZ, t_(2), t_(6))])
+    r.lin([(RY, [T(t_(10)), T(t_(11), -1, 3)])])                                   # Y' = g^2 - 3 e^2
+
+    # ---- mixed addition step (src/groups/mod.rs:731-752): R += the affine point at base B (x, y); line into L
+    r = new("ADD")
+    bx, by = B, B + 1
+    r.mul([(t_(0), RZ, bx), (t_(1), RZ, by)])
+    r.lin([(t_(2), [T(RX), T(t_(0), -1)]), (t_(3), [T(RY), T(t_(1), -1)]),          # d, e
+           (LVW, [T(RX), T(t_(0), -1)]), (LVV, [T(RY, -1), T(t_(1))])])             # ell_vw = d, ell_vv = -e
+    r.mul([(t_(4), t_(2), t_(2)), (t_(5), t_(3), t_(3)), (t_(6), t_(3), bx), (t_(7), t_(2), by)])   # f, g, e x, d y
+    r.mul([(t_(8), t_(2), t_(4)), (t_(9), RX, t_(4)), (t_(10), RZ, t_(5))])         # h, i, Z g
+    r.lin([(t_(11), [T(t_(10)), T(t_(8)), T(t_(9), -1, 2)]),                        # j = Z g + h - 2 i
+           (t_(12), [T(t_(9), 1, 3), T(t_(10), -1), T(t_(8), -1)]),                 # i - j
+           (L0, [T(t_(6), 1, 1, 1), T(t_(7), -1, 1, 1)])])                          # ell_0 = xi (e x - d y)
+    r.mul([(RX, t_(2), t_(11)), (t_(13), t_(3), t_(12)), (t_(14), t_(8), RY), (RZ, RZ, t_(8))])
+    r.lin([(RY, [T(t_(13)), T(t_(14), -1)])])
+
+    # ---- pi(Q), -pi^2(Q) (AffineG2::mul_by_q, src/groups/mod.rs:694-699, :718-726)
+    r = new("FROBQ")
+    r.mul([(Q1, QA, C_TWQX, True, False), (Q1 + 1, QA + 1, C_TWQY, True, False)])
+    r.mul([(Q2, Q1, C_TWQX, True, False), (Q2 + 1, T(Q1 + 1, -1), C_TWQY, True, False)])
+
+    # ---- f <- f * line(P) (src/groups/mod.rs:589 + Fq12::mul_by_024, src/fields/fq12.rs:130-196) as six 3-term sums
+    r = new("LINE")
+    r.mul([(X2, LVV, PA), (X4, LVW, PA + 1)])
+    z = [F + i for i in range(6)]
+    x0, x2, x4 = L0, X2, X4
+    prods = [(z[0], x0), (z[1], x2), (z[4], x4),      # z0' = z0 x0 + xi (z1 x2 + z4 x4)
+             (z[1], x0), (z[5], x4), (z[2], x2),      # z1' = z1 x0 + xi (z5 x4 + z2 x2)
+             (z[2], x0), (z[0], x2), (z[3], x4),      # z2' = z2 x0 + z0 x2 + z3 x4
+             (z[3], x0), (z[2], x4), (z[4], x2),      # z3' = z3 x0 + xi (z2 x4 + z4 x2)
+             (z[4], x0), (z[0], x4), (z[5], x2),      # z4' = z4 x0 + z0 x4 + xi z5 x2
+             (z[5], x0), (z[3], x2), (z[1], x4)]      # z5' = z5 x0 + z3 x2 + z1 x4
+    r.mul([(t_(i), a, b) for i, (a, b) in enumerate(prods)])
+    p = [T(t_(i)) for i in range(18)]
+    r.lin([(z[0], [p[0], xi(p[1]), xi(p[2])]), (z[1], [p[3], xi(p[4]), xi(p[5])]), (z[2], [p[6], p[7], p[8]]),
+           (z[3], [p[9], xi(p[10]), xi(p[11])]), (z[4], [p[12], p[13], xi(p[14])]), (z[5], [p[15], p[16], p[17]])])
+
+    # ---- f <- f^2, complex method (src/fields/fq12.rs:295-303)
+    r = new("SQR12")
+    r.lin([(t_(0), [T(z[0]), xi(T(z[5]))]), (t_(1), [z[1], z[3]]), (t_(2), [z[2], z[4]])])      # a0 + v a1
+    r.mul(fq6_products(t_(3), [z[0], z[1], z[2]], [z[3], z[4], z[5]]) +                          # ab = a0 a1
+          fq6_products(t_(9), [[z[0], z[3]], [z[1], z[4]], [z[2], z[5]]], [t_(0), t_(1), t_(2)]))   # (a0 + a1)(a0 + v a1)
+    oa, ot = fq6_outputs(t_(3)), fq6_outputs(t_(9))
+    r.lin([(t_(15 + i), oa[i]) for i in range(3)] + [(t_(18 + i), ot[i]) for i in range(3)])
+    ab, tt = [T(t_(15 + i)) for i in range(3)], [T(t_(18 + i)) for i in range(3)]
+    r.lin([(z[0], [tt[0], neg(ab[0]), xi(neg(ab[2]))]), (z[1], [tt[1], neg(ab[1]), neg(ab[0])]), (z[2], [tt[2], neg(ab[2]), neg(ab[1])]),
+           (z[3], times(ab[0], 2)), (z[4], times(ab[1], 2)), (z[5], times(ab[2], 2))])
+
+    # ---- D <- A * B and D <- A * conj(B) (src/fields/fq12.rs:316-328; conj = unitary_inverse :126-128).  D may alias A or B.
+    for name, s in (("MUL12", 1), ("MUL12C", -1)):
+        r = new(name)
+        a, b = [A + i for i in range(6)], [B + i for i in range(6)]
+        r.mul(fq6_products(t_(0), a[0:3], b[0:3]) +
+              fq6_products(t_(6), a[3:6], [T(b[3 + i], s) for i in range(3)]) +
+              fq6_products(t_(12), [[a[i], a[3 + i]] for i in range(3)], [[T(b[i]), T(b[3 + i], s)] for i in range(3)]))
+        outs = fq6_outputs(t_(0)) + fq6_outputs(t_(6)) + fq6_outputs(t_(12))
+        r.lin([(t_(18 + k), outs[k]) for k in range(9)])
+        aa, bb, cc = ([T(t_(18 + 3 * k + i)) for i in range(3)] for k in range(3))
+        r.lin([(D + 0, [aa[0], xi(bb[2])]), (D + 1, [aa[1], bb[0]]), (D + 2, [aa[2], bb[1]])] +
+              [(D + 3 + i, [cc[i], neg(aa[i]), neg(bb[i])]) for i in range(3)])
+
+    # ---- D <- cyclotomic_squared(A) (src/fields/fq12.rs:198-247): three Fq4 squarings as a^2, b^2, (a + b)^2.  In place allowed.
+    r = new("CYC")
+    a = [A + i for i in range(6)]
+    pairs = [(a[0], a[4]), (a[3], a[2]), (a[1], a[5])]          # (z0, z1), (z2, z3), (z4, z5) in the reference's labels
+    lanes = []
+    for k, (u, v) in enumerate(pairs):
+        lanes += [(t_(3 * k), u, u), (t_(3 * k + 1), v, v), (t_(3 * k + 2), [u, v], [u, v])]
+    r.mul(lanes)
+
+    def t0(k, old):      # 3 (a^2 + xi b^2) - 2 old
+        return [T(t_(3 * k), 1, 3), T(old, -1, 2), T(t_(3 * k + 1), 1, 3, 1)]
+
+    def t1(k, old, with_xi):   # 3 (2ab) + 2 old, 2ab = (a + b)^2 - a^2 - b^2, times xi for the last pair
+        g = 1 if with_xi else 0
+        return [T(t_(3 * k + 2), 1, 3, g), T(t_(3 * k), -1, 3, g), T(t_(3 * k + 1), -1, 3, g), T(old, 1, 2)]
+    r.lin([(D + 0, t0(0, a[0])), (D + 4, t1(0, a[4], False)),
+           (D + 1, t0(1, a[1])), (D + 5, t1(1, a[5], False)),
+           (D + 2, t0(2, a[2])), (D + 3, t1(2, a[3], True))])
+
+    # ---- D <- conj(A), D <- A
+    r = new("CONJ12")
+    r.lin([(D + i, T(A + i, 1 if i < 3 else -1)) for i in range(6)])
+    r = new("COPY12")
+    r.lin([(D + i, A + i) for i in range(6)])
+
+    # ---- D <- frobenius_map(A, p) (src/fields/fq12.rs:112-119, fq6.rs:125-131).  In place allowed.
+    for p in (1, 2, 3):
+        r = new("FROB%d" % p)
+        cj = bool(p & 1)
+        r.mul([(D + 0, A + 0, ONE, cj, False), (D + 1, A + 1, C_F6C1[p], cj, False), (D + 2, A + 2, C_F6C2[p], cj, False),
+               (t_(0), A + 3, ONE, cj, False), (t_(1), A + 4, C_F6C1[p], cj, False), (t_(2), A + 5, C_F6C2[p], cj, False)])
+        r.mul([(D + 3 + i, t_(i), C_F12C[p]) for i in range(3)])
+
+    # ---- D <- A^-1 (src/fields/fq12.rs:305-313 -> fq6.rs:179-191 -> fq2.rs:119-130; the Fq inversion is Fermat, same element)
+    r = new("INV12")
+    a = [A + i for i in range(6)]
+    r.mul(fq6_products(t_(0), a[0:3], a[0:3]) + fq6_products(t_(6), a[3:6], a[3:6]))
+    o0, o1 = fq6_outputs(t_(0)), fq6_outputs(t_(6))
+    r.lin([(t_(12 + i), o0[i]) for i in range(3)] + [(t_(15 + i), o1[i]) for i in range(3)])
+    r.lin([(t_(18), [T(t_(12)), xi(T(t_(17), -1))]), (t_(19), [T(t_(13)), T(t_(15), -1)]), (t_(20), [T(t_(14)), T(t_(16), -1)])])
+    g0, g1, g2 = t_(18), t_(19), t_(20)                           # t = a0^2 - v a1^2
+    r.mul([(t_(21), g0, g0), (t_(22), g1, g2), (t_(23), g2, g2), (t_(24), g0, g1), (t_(25), g1, g1), (t_(26), g0, g2)])
+    r.lin([(t_(27), [T(t_(21)), xi(T(t_(22), -1))]), (t_(28), [xi(T(t_(23))), T(t_(24), -1)]), (t_(29), [T(t_(25)), T(t_(26), -1)])])
+    r.mul([(t_(30), g2, t_(28)), (t_(31), g1, t_(29)), (t_(32), g0, t_(27))])
+    r.lin([(t_(33), [T(t_(32)), xi(T(t_(30))), xi(T(t_(31)))])])
+    r.mul([(t_(34), t_(33), t_(33), False, True)])                # norm
+    r.inv(t_(35), t_(34))
+    r.mul([(t_(36), t_(33), t_(35), True, False)])                # conj / norm
+    r.mul([(t_(37 + i), t_(36), t_(27 + i)) for i in range(3)])   # u = t^-1 (Fq6)
+    u = [t_(37), t_(38), t_(39)]
+    r.mul(fq6_products(t_(0), a[0:3], u) + fq6_products(t_(6), a[3:6], u))
+    o0, o1 = fq6_outputs(t_(0)), fq6_outputs(t_(6))
+    r.lin([(D + i, o0[i]) for i in range(3)] + [(D + 3 + i, [neg(t) for t in o1[i]]) for i in range(3)])
+    return R
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# programs (call lists)
+# ------------------------------------------------------------------------------------------------------------------
+def wnaf4(k):
+    """Width-4 signed-window digits of k, least significant first: odd digits in -7..7, at most one in any 4 positions."""
+    d = []
+    while k:
+        if k & 1:
+            z = k & 15
+            if z > 8:
+                z -= 16
+            k -= z
+        else:
+            z = 0
+        d.append(z)
+        k >>= 1
+    return d
+
+
+def build_program():
+    """Returns (calls, marks): calls = [(routine, baseD, baseA, baseB)], marks = index ranges of the phases."""
+    calls = []
+
+    def call(name, d=0, a=0, b=0):
+        calls.append((name, d, a, b))
+
+    marks = {}
+    # ---- Miller loop with the line coefficients produced on the fly (AffineG2::precompute + G2Precomp::miller_loop)
+    marks["pairing_begin"] = len(calls)
+    call("TOAFF")
+    marks["miller_begin"] = len(calls)
+    naf = o.ATE_LOOP_COUNT_NAF
+    assert len(naf) == 64
+    for k, dg in enumerate(naf):
+        if k:
+            call("SQR12")                   # the reference squares 1 in the first iteration: same value
+        call("DBL")
+        call("LINE")
+        if dg:
+            call("ADD", 0, 0, (QA if dg == 1 else QN).off)
+            call("LINE")
+    call("FROBQ")
+    call("ADD", 0, 0, Q1.off)
+    call("LINE")
+    call("ADD", 0, 0, Q2.off)
+    call("LINE")
+    marks["miller_end"] = len(calls)
+    # ---- final exponentiation (src/fields/fq12.rs:62-110) on the Fq12 registers
+    marks["fexp_begin"] = len(calls)
+    X, RA, RB, RC, RD, RE, RF, RG, CUR, A3, A5, A7, TT = (ereg(k) for k in range(13))
+    f = F.off
+    # easy part: x = frob2(c) c, c = conj(f) f^-1
+    call("INV12", RB, f)
+    call("MUL12C", RC, RB, f)               # c = f^-1 conj(f)
+    call("FROB2", RA, RC)
+    call("MUL12", X, RA, RC)
+    marks["hard_begin"] = len(calls)
+
+    digits = wnaf4(o.BN_U)
+    assert sum(dg << i for i, dg in enumerate(digits)) == o.BN_U and digits[-1] == 1
+    tab = {3: A3, 5: A5, 7: A7}
+
+    def exp_by_neg_z(dst, a):
+        """dst = conj(a^u), width-4 signed window (csrc/bn_tower.cuh fq12_exp_by_neg_z; value of src/fields/fq12.rs:121-124)."""
+        call("CYC", CUR, a)                 # a^2: serves the table and, the top digit being +1, the first doubling
+        call("MUL12", A3, CUR, a)
+        call("MUL12", A5, CUR, A3)
+        call("MUL12", A7, CUR, A5)
+        tab[1] = a
+        first = True
+        for i in range(len(digits) - 2, -1, -1):
+            if not first:
+                call("CYC", CUR, CUR)
+            first = False
+            dg = digits[i]
+            if dg:
+                call("MUL12" if dg > 0 else "MUL12C", CUR, CUR, tab[abs(dg)])
+        call("CONJ12", dst, CUR)
+
+    exp_by_neg_z(RA, X)                     # a
+    call("CYC", RB, RA)                     # b
+    call("CYC", RC, RB)                     # c
+    call("MUL12", RD, RC, RB)               # d
+    exp_by_neg_z(RE, RD)                    # e
+    call("CYC", RF, RE)                     # f
+    exp_by_neg_z(RG, RF)                    # g
+    call("MUL12C", RA, RE, RG)              # j = conj(g) e
+    call("MUL12C", RC, RA, RD)              # k = j conj(d)
+    call("MUL12", RF, RC, RB)               # l = k b
+    call("MUL12", RA, RC, RE)               # m = k e
+    call("MUL12", RG, X, RA)                # n = x m
+    call("FROB1", RA, RF)                   # o
+    call("MUL12", RB, RA, RG)               # p = o n
+    call("FROB2", RA, RC)                   # q
+    call("MUL12", RG, RA, RB)               # r = q p
+    call("MUL12C", RA, RF, X)               # t = conj(x) l
+    call("FROB3", RB, RA)                   # u
+    call("MUL12", f, RB, RG)                # v = u r  -> the result slots
+    marks["fexp_end"] = len(calls)
+    marks["pairing_end"] = len(calls)
+    return calls, marks
+
+
+def constants():
+    """Values of the constant slots (canonical Fq2 tuples)."""
+    c = {ZERO.off: (0, 0), ONE.off: (1, 0), C_B3.off: o.fq2_scale(o.G2_B, 3), C_TWQX.off: o.TWIST_MUL_BY_Q_X, C_TWQY.off: o.TWIST_MUL_BY_Q_Y}
+    for p in (1, 2, 3):
+        c[C_F6C1[p].off] = o.FQ6_FROB_C1[p]
+        c[C_F6C2[p].off] = o.FQ6_FROB_C2[p]
+        c[C_F12C[p].off] = o.FQ12_FROB_C1[p]
+    return c
+
+
+def fresh_slots():
+    slots = [(0, 0)] * N_SLOTS
+    for k, v in constants().items():
+        slots[k] = v
+    return slots
+
+
+def get_f12(slots, base):
+    s = slots[base:base + 6]
+    return ((s[0], s[1], s[2]), (s[3], s[4], s[5]))
+
+
+def put_f12(slots, base, v):
+    for i in range(6):
+        slots[base + i] = v[i // 3][i % 3]
+
+
+def simulate(p, q, phase="pairing"):
+    """Run the program on Jacobian points p (G1) and q (G2) given as canonical integer tuples.  Returns the Fq12 in the result
+    slots (phase 'miller': the un-exponentiated value)."""
+    R = build_routines()
+    calls, marks = build_program()
+    slots = fresh_slots()
+    for i in range(3):
+        slots[IN_P.off + i] = (p[i] % Q, 0)
+        slots[IN_Q.off + i] = q[i]
+    lo = marks["pairing_begin"]
+    hi = marks["miller_end"] if phase == "miller" else marks["pairing_end"]
+    run_program(slots, R, calls[lo:hi])
+    return get_f12(slots, F.off)
+
+
+def simulate_fexp(x):
+    R = build_routines()
+    calls, marks = build_program()
+    slots = fresh_slots()
+    put_f12(slots, F.off, x)
+    run_program(slots, R, calls[marks["fexp_begin"]:marks["fexp_end"]])
+    return get_f12(slots, F.off)
