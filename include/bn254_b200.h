@@ -146,6 +146,16 @@ int bn254_miller_product(bn254_ctx* ctx, const void* g1, const void* g2, size_t 
 /* Gt::final_exponentiation -> Option<Gt>: some[i] = 0 (and gt_out = 0) iff the input is zero */
 int bn254_final_exp_many(bn254_ctx* ctx, const void* gt_in, void* gt_out, uint8_t* some, size_t n);
 int bn254_final_exp_many_dev(bn254_ctx* ctx, const void* d_gt_in, void* d_gt_out, uint8_t* d_some, size_t n);
+/* Same as bn254_final_exp_many_dev for n <= BN254_NOALLOC_MAX_N, allocating NOTHING: no cudaMalloc, cudaFree or allocating
+ * library routine on any call.  No counterpart in the reference: added for callers
+ * that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The easy part's
+ * intermediate values live in a static device array of the library (BN254_NOALLOC_MAX_N x 385 bytes = 1.5 MB, held by every
+ * GPU that loads the library until exit) instead of the context's grow-only workspace.  n > BN254_NOALLOC_MAX_N returns
+ * BN254_ERR_ARG.  All calls on one device share that array: calls that overlap on the GPU (two contexts of one device) race;
+ * calls of one context are stream-ordered and safe.  Enqueues on the context's stream without synchronising; d_gt_out may
+ * alias d_gt_in; d_some may be NULL. */
+#define BN254_NOALLOC_MAX_N 4096
+int bn254_final_exp_many_dev_noalloc(bn254_ctx* ctx, const void* d_gt_in, void* d_gt_out, uint8_t* d_some, size_t n);
 int bn254_gt_mul_many(bn254_ctx* ctx, const void* a, const void* b, void* out, size_t n);     /* Gt * Gt   */
 int bn254_gt_pow_many(bn254_ctx* ctx, const void* a, const void* fr, void* out, size_t n);    /* Gt::pow   */
 int bn254_gt_inverse_many(bn254_ctx* ctx, const void* a, void* out, uint8_t* some, size_t n); /* Gt::inverse */

@@ -227,6 +227,7 @@ void bn254_ctx_destroy(bn254_ctx* ctx) {
     delete ctx;
 }
 
+static void noalloc_setup(int device);   // no-alloc entry point (end of this file): resolves its static scratch, never fails the context
 static int ctx_init(bn254_ctx* c, int device, const bn254_ctx_options* user) {
     c->device = device;
     bn254_ctx_options_default(&c->opt);
@@ -261,6 +262,7 @@ static int ctx_init(bn254_ctx* c, int device, const bn254_ctx_options* user) {
     CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
+    noalloc_setup(device);
     // The call graph is static (no recursion, no indirect calls; largest frame 8 KB in ptxas.log), so the driver sizes the
     // stack of every launch itself.  Only an explicit request touches the device-wide limit, and only upwards.
     if (c->opt.stack_bytes > 0) {
@@ -1400,3 +1402,58 @@ int bn254_microbench(bn254_ctx* ctx, int kind, int grid, int block, int iters, d
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// bn254_final_exp_many_dev_noalloc: the final exponentiation with its scratch in a static device array.
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  The regular entry point keeps the easy part's values
+// and Option flags in the context's grow-only workspace (cudaMalloc on growth); this one keeps them here.
+//
+// Every GPU that loads the library holds the array until exit: BN254_NOALLOC_MAX_N x (384 + 1) bytes = 1.5 MB.
+// All calls on a device SHARE it and it keeps the last call's contents.  Nothing in it has to start at zero: the easy-part
+// kernel writes value i and flag i for every i < n before the hard-part kernel, ordered behind it on the same stream, reads
+// them, and no kernel reads an index >= n.  Calls that overlap on the GPU (two contexts / streams of one device) race on it.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char bn254_noalloc_scratch[(size_t)BN254_NOALLOC_MAX_N * (sizeof(Fq12) + 1)];
+
+// In host code the array's name is a host-side stand-in, not a device address: the address the kernels get comes from
+// cudaGetSymbolAddress, taken once per device with that device current (context set-up) and cached here.
+static const int NOALLOC_MAX_DEVICES = 64;
+static void* g_noalloc_addr[NOALLOC_MAX_DEVICES];
+static cudaError_t g_noalloc_err[NOALLOC_MAX_DEVICES];
+static bool g_noalloc_done[NOALLOC_MAX_DEVICES];
+static std::mutex g_noalloc_mu;
+static void noalloc_setup(int device) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return;
+    std::lock_guard<std::mutex> g(g_noalloc_mu);
+    if (g_noalloc_done[device]) return;
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&ptr, bn254_noalloc_scratch);
+    g_noalloc_err[device] = e;
+    g_noalloc_addr[device] = e == cudaSuccess ? ptr : nullptr;
+    g_noalloc_done[device] = true;
+    if (e != cudaSuccess) cudaGetLastError();   // reported by the entry point, not by bn254_ctx_create
+}
+
+extern "C" int bn254_final_exp_many_dev_noalloc(bn254_ctx* ctx, const void* d_gt_in, void* d_gt_out, uint8_t* d_some, size_t n) {
+    API_BEGIN
+    ENTER(ctx);
+    if (n == 0) return 0;
+    if (n > (size_t)BN254_NOALLOC_MAX_N)
+        return fail(BN254_ERR_ARG, "bn254_final_exp_many_dev_noalloc: n exceeds BN254_NOALLOC_MAX_N (the static scratch holds 4096 values); "
+                                   "split the batch or use bn254_final_exp_many_dev");
+    if (!d_gt_in || !d_gt_out) return fail(BN254_ERR_ARG, "null pointer");
+    CHECK_ALIGNED(d_gt_in, d_gt_out);
+    if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES) return fail(BN254_ERR_ARG, "device index beyond the no-alloc table");
+    void* scratch = g_noalloc_addr[ctx->device];
+    if (!scratch) return fail(BN254_ERR_CUDA, "cudaGetSymbolAddress(bn254_noalloc_scratch)", g_noalloc_err[ctx->device]);
+    if (ctx->opt.fexp_smem != 2) return fail(BN254_ERR_ARG, "the no-alloc variant runs the default (fexp_smem = 2) kernels only");
+    Lane L = main_lane(ctx);
+    Fq12* t = (Fq12*)scratch;                                                   // easy-part values
+    uint8_t* flags = (uint8_t*)scratch + (size_t)BN254_NOALLOC_MAX_N * sizeof(Fq12);   // Option flags of the easy part
+    LAUNCH(L, k_final_exp_easy, n, (const Fq12*)d_gt_in, t, flags, n);
+    unsigned bs = sync_block(L, n), g = (unsigned)((n + bs - 1) / bs);
+    LAUNCH_SYNC(L, k_final_exp_hard_sync, g, bs, sync_smem(bs), (const Fq12*)t, (const uint8_t*)flags, (Fq12*)d_gt_out, d_some, (uint8_t*)nullptr, n);
+    return 0;
+    API_END
+}
