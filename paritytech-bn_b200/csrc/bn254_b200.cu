@@ -17,9 +17,6 @@
 
 using namespace bn;
 
-#ifndef BN_HAVE_COOP
-#define BN_COOP_DEFAULT_MAX_N 0
-#endif
 
 static_assert(sizeof(Fq) == 32 && sizeof(Fq2) == 64 && sizeof(Fq12) == 384, "repr(C) sizes");
 static_assert(sizeof(G1) == 96 && sizeof(G2) == 192 && sizeof(EllCoeffs) == 192, "repr(C) sizes");
@@ -254,6 +251,7 @@ static int ctx_init(bn254_ctx* c, int device, const bn254_ctx_options* user) {
     } else if (c->opt.fexp_smem == 2) {
         CU(cudaFuncSetAttribute(k_final_exp_hard_sync, cudaFuncAttributeMaxDynamicSharedMemorySize, smem7));
     }
+    CU(cudaFuncSetAttribute(k_coop_pairing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BN_COOP_SMEM(BN_COOP_MAX_WARPS)));
     // the main stream outranks the second one: in the pipelined path the first half batch gets ahead of the second
     int prio_least = 0, prio_greatest = 0;
     cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
@@ -306,9 +304,23 @@ uint64_t bn254_ctx_launch_count(const bn254_ctx* ctx) { return ctx ? ctx->launch
 
 #define ENTER(ctx) TRY(use(ctx)); std::lock_guard<std::recursive_mutex> _guard((ctx)->mu)
 
+// Warp-cooperative latency path (bn_coop.cuh): one warp per pairing, for batches too small to fill the machine with one
+// thread per pairing.  Same bytes as the throughput path.
+static inline bool use_coop(const bn254_ctx* ctx, size_t n) { return ctx->opt.coop_max_n > 0 && n <= (size_t)ctx->opt.coop_max_n; }
+// mode 0: pairing, 1: Miller value (+ ok flags), 2: final exponentiation (g1 = the Gt input; ok = Option flags)
+static int coop_pairing_dev(const Lane& L, const void* d_g1, const G2* d_g2, Fq12* d_out, uint8_t* d_ok, size_t n, int mode,
+                            uint8_t* d_is_one = nullptr) {
+    size_t per_sm = (n + (size_t)L.ctx->sms - 1) / (size_t)L.ctx->sms;
+    unsigned warps = per_sm < 1 ? 1u : per_sm > BN_COOP_MAX_WARPS ? (unsigned)BN_COOP_MAX_WARPS : (unsigned)per_sm;
+    unsigned g = (unsigned)((n + warps - 1) / warps);
+    LAUNCH_SYNC(L, k_coop_pairing, g, warps * 32, BN_COOP_SMEM(warps), d_g1, d_g2, d_out, d_ok, d_is_one, n, mode);
+    return 0;
+}
+
 // final exponentiation of n values (in place allowed): single kernel, or easy + hard kernels
 static int final_exp_dev(const Lane& L, const Fq12* d_in, Fq12* d_out, uint8_t* d_some, uint8_t* d_is_one, size_t n) {
     const bn254_ctx_options& o = L.ctx->opt;
+    if (use_coop(L.ctx, n)) return coop_pairing_dev(L, d_in, (const G2*)nullptr, d_out, d_some, n, 2, d_is_one);
     if (!o.split_fexp && !o.fexp_smem) {
         LAUNCH(L, k_final_exp_many, n, d_in, d_out, d_some, d_is_one, n);
         return 0;
@@ -380,6 +392,7 @@ static int miller_ws(const Lane& L, size_t n, MillerWs& w) {
 // accumulates the per-kernel times of every chunk (synchronises per chunk: profiling twin only).
 static int miller_many_dev(const Lane& L, const G2* d_g2, const G1* d_g1, Fq12* d_f, uint8_t* d_ok, size_t n,
                            cudaEvent_t* ev = nullptr, float* ms = nullptr) {
+    if (!ev && use_coop(L.ctx, n)) return coop_pairing_dev(L, d_g1, d_g2, d_f, d_ok, n, 1);
     if (L.ctx->opt.fused_miller) {
         if (ev) CU(cudaEventRecord(ev[0], L.stream));
         LAUNCH(L, k_miller_many, n, d_g2, d_g1, d_f, d_ok, n);
@@ -408,20 +421,6 @@ static int miller_many_dev(const Lane& L, const G2* d_g2, const G1* d_g1, Fq12* 
     }
     return 0;
 }
-// Warp-cooperative latency path (bn_coop.cuh): one warp per pairing, for batches too small to fill the machine with one
-// thread per pairing.  Same bytes as the throughput path.
-static inline bool use_coop(const bn254_ctx* ctx, size_t n) { return ctx->opt.coop_max_n > 0 && n <= (size_t)ctx->opt.coop_max_n; }
-#ifdef BN_HAVE_COOP
-static int coop_pairing_dev(const Lane& L, const G1* d_g1, const G2* d_g2, Fq12* d_out, size_t n, int mode) {
-    unsigned warps = BN_COOP_WARPS;
-    unsigned g = (unsigned)((n + warps - 1) / warps);
-    LAUNCH_SYNC(L, k_coop_pairing, g, warps * 32, (size_t)warps * BN_COOP_SMEM_PER_WARP, d_g1, d_g2, d_out, n, mode);
-    return 0;
-}
-#else
-static int coop_pairing_dev(const Lane&, const G1*, const G2*, Fq12*, size_t, int) { return fail(BN254_ERR_ARG, "latency path not built"); }
-#endif
-
 // reduce n Fq12 values in `a` to one product; `b` is scratch of >= (n+1)/2 elements.  Result pointer returned.
 static int tree_product(const Lane& L, Fq12* a, Fq12* b, size_t n, Fq12** result) {
     Fq12 *src = a, *dst = b;
@@ -459,7 +458,7 @@ int bn254_pairing_many_dev(bn254_ctx* ctx, const void* d_g1, const void* d_g2, v
     if (!d_g1 || !d_g2 || !d_gt_out) return fail(BN254_ERR_ARG, "null pointer");
     CHECK_ALIGNED(d_g1, d_g2, d_gt_out);
     Lane L = main_lane(ctx);
-    if (use_coop(ctx, n)) return coop_pairing_dev(L, (const G1*)d_g1, (const G2*)d_g2, (Fq12*)d_gt_out, n, 0);
+    if (use_coop(ctx, n)) return coop_pairing_dev(L, d_g1, (const G2*)d_g2, (Fq12*)d_gt_out, (uint8_t*)nullptr, n, 0);
     // Miller values are written to the output buffer and exponentiated in place
     TRY(miller_many_dev(L, (const G2*)d_g2, (const G1*)d_g1, (Fq12*)d_gt_out, (uint8_t*)nullptr, n));
     TRY(final_exp_dev(L, (const Fq12*)d_gt_out, (Fq12*)d_gt_out, (uint8_t*)nullptr, (uint8_t*)nullptr, n));
@@ -519,7 +518,7 @@ static int pairing_many_enqueue(const Lane& L, const char* g1, const char* g2, c
     TRY(h2d(L, dg1, g1 + lo * sizeof(G1), m * sizeof(G1)));
     TRY(h2d(L, dg2, g2 + lo * sizeof(G2), m * sizeof(G2)));
     if (use_coop(L.ctx, m)) {
-        TRY(coop_pairing_dev(L, dg1, dg2, mapped ? (Fq12*)mapped + lo : df, m, 0));
+        TRY(coop_pairing_dev(L, dg1, dg2, mapped ? (Fq12*)mapped + lo : df, (uint8_t*)nullptr, m, 0));
         if (!mapped) TRY(d2h(L, gt_out + lo * sizeof(Fq12), df, m * sizeof(Fq12)));
         return 0;
     }
@@ -652,6 +651,11 @@ int bn254_miller_loop_many(bn254_ctx* ctx, const void* g2, const void* g1, void*
 // ---------------------------------------------------------------------------------------------
 // product checks (pairing_batch) and miller_loop_batch
 // ---------------------------------------------------------------------------------------------
+// product checks that run as independent Miller loops + a per-check product: more than 8 pairs per check, or a batch small
+// enough for the warp-cooperative path (no shared tables)
+static inline bool indep_products(const bn254_ctx* ctx, size_t v, size_t m, size_t n_checks) {
+    return v > 8 || (m == 0 && v > 0 && use_coop(ctx, n_checks * v));
+}
 // Miller products of n_checks checks into d_f (n_checks x Fq12); shared tables optional
 static int miller_products_dev(const Lane& L, const G1* d_g1v, const G2* d_g2v, size_t v, const G1* d_g1s,
                                const bn254_g2precomp* pc, size_t n_checks, Fq12* d_f) {
@@ -659,8 +663,9 @@ static int miller_products_dev(const Lane& L, const G1* d_g1v, const G2* d_g2v, 
     size_t m = pc ? pc->n : 0;
     const uint4* tab = pc ? pc->tab : nullptr;
     if (m > 8) return fail(BN254_ERR_ARG, "at most 8 shared tables per check");
-    if (v > 8) {
-        // many pairs per check: independent Miller loops, then a per-check product (same field element)
+    if (indep_products(ctx, v, m, n_checks)) {
+        // many pairs per check, or a batch small enough for the warp-cooperative path: independent Miller loops, then a
+        // per-check product (same field element)
         if (m != 0) return fail(BN254_ERR_ARG, "more than 8 variable pairs cannot be combined with shared tables");
         size_t sz[1] = {n_checks * v * sizeof(Fq12)};
         void* tmp[1];
@@ -726,7 +731,7 @@ static int product_checks_dev(bn254_ctx* ctx, const bn254_g2precomp* pc, const v
     Fq12* d_f = (Fq12*)d_gt_out;
     if (!d_f) {
         // the v > 8 path carves the aux arena as well: take both regions in one carve
-        size_t sz[2] = {v > 8 ? n_checks * v * sizeof(Fq12) : 0, n_checks * sizeof(Fq12)};
+        size_t sz[2] = {indep_products(ctx, v, pc ? pc->n : 0, n_checks) ? n_checks * v * sizeof(Fq12) : 0, n_checks * sizeof(Fq12)};
         void* t[2];
         TRY(ctx_aux(ctx, sz, 2, t));
         d_f = (Fq12*)t[1];

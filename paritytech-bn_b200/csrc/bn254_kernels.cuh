@@ -6,6 +6,7 @@
 #include "bn_wire.cuh"
 #include "bn_slots.cuh"
 #include "bn_slots_curve.cuh"
+#include "bn_coop.cuh"
 
 namespace bn {
 

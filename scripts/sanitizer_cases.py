@@ -13,16 +13,20 @@ from oracle import c_oracle as c  # noqa: E402
 from tests import util  # noqa: E402
 
 sizes = [int(x) for x in sys.argv[1:]] or [8, 449, 1600]
-eng = bn.Engine(0)
+eng = bn.Engine(0, coop_max_n=0)          # the slot-file kernels (one thread per pairing) at small sizes
+coop = bn.Engine(0)                       # default: batches this small run one warp per pairing (k_coop_pairing)
 for n in sizes:
     g1, g2 = util.points_cpu(util.scalars(n, stream=71), util.scalars(n, stream=72))
     g1 = g1.reshape(n, 96).copy()
     g1[min(3, n - 1)] = util.G1_INF
     g1 = g1.reshape(-1)
-    got = eng.pairing(g1, g2)
     m = min(n, 64)
-    assert got[:m * 384].tobytes() == c.pairing_many(g1[:m * 96], g2[:m * 192]).tobytes(), n
-    print("pairing n=%d ok" % n, flush=True)
+    exp = c.pairing_many(g1[:m * 96], g2[:m * 192]).tobytes()
+    for name, e in (("slot-file", eng), ("warp-cooperative", coop)):
+        got = e.pairing(g1, g2)
+        assert got[:m * 384].tobytes() == exp, (name, n)
+        print("pairing n=%d %s ok" % (n, name), flush=True)
+coop.close()
 w = util.groth16_checks(70)
 out, is_one = eng.pairing_batch(w["g1"], w["g2"], pairs_per_check=4)
 rout, ris = c.pairing_product_many(w["g1"], w["g2"], 4)

@@ -1,0 +1,52 @@
+"""The microcode of the warp-cooperative pairing (tools/gen_coop_ucode.py -> csrc/bn_coop_ucode.cuh) on the CPU: the
+generator's simulator runs the very tables the GPU executes, on Python integers, against the oracle."""
+import os
+import random
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+import gen_coop_ucode as g  # noqa: E402
+
+from oracle import bn254_ref as o  # noqa: E402
+
+rng = random.Random(77)
+
+
+def _pair():
+    p = o.g_mul(o.FQ_OPS, o.G1_ONE, rng.randrange(1, o.R_ORDER))
+    q = o.g_mul(o.FQ2_OPS, o.G2_ONE, rng.randrange(1, o.R_ORDER))
+    return p, q
+
+
+def test_miller_and_pairing_match_the_oracle():
+    for _ in range(2):
+        p, q = _pair()
+        pa, qa = o.g_to_affine(o.FQ_OPS, p), o.g_to_affine(o.FQ2_OPS, q)
+        assert g.simulate(p, q, "miller") == o.miller_loop(o.g2_precompute(qa), pa)
+        assert g.simulate(p, q) == o.pairing(p, q)
+    # z == 1 inputs (the generators) go the same way
+    assert g.simulate(o.G1_ONE, o.G2_ONE) == o.pairing(o.G1_ONE, o.G2_ONE)
+
+
+def test_final_exponentiation_phase_alone():
+    p, q = _pair()
+    f = g.simulate(p, q, "miller")
+    assert g.simulate_fexp(f) == o.fq12_final_exponentiation(f)
+
+
+def test_encoded_tables_decode_to_the_same_result():
+    """What is emitted (16-bit terms, lane words, headers, trace) is what was simulated."""
+    p, q = _pair()
+    assert g.decode_and_run(p, q) == o.pairing(p, q)
+
+
+def test_committed_header_is_up_to_date(tmp_path):
+    out = tmp_path / "ucode.cuh"
+    g.emit(str(out))
+    assert out.read_text() == open(os.path.join(ROOT, "paritytech-bn_b200", "csrc", "bn_coop_ucode.cuh")).read()
+
+
+def test_window_digits_reconstruct_u():
+    d = g.wnaf4(o.BN_U)
+    assert sum(x << i for i, x in enumerate(d)) == o.BN_U and all(x == 0 or (x % 2 and -7 <= x <= 7) for x in d)

@@ -399,6 +399,57 @@ def test_abi_smoke_compiled_c_consumer():
     assert "abi_smoke ok" in p.stdout
 
 
+@pytest.mark.parametrize("n", [1, 3, 17, 149, 2368])
+def test_warp_cooperative_latency_path(eng, n):
+    """Batches of at most coop_max_n pairings run one WARP per pairing (k_coop_pairing executing the generated microcode):
+    pairing, miller_loop_many, final_exponentiation (incl. zero -> None) and small pairing_batch products give the oracle's
+    bytes, the same bytes as the one-thread-per-pairing kernels (coop_max_n = 0), with points at infinity and z == 1."""
+    import paritytech_bn_b200 as bn
+    base = min(n, 256)
+    p1, p2 = util.points_cpu(util.scalars(base, stream=91), util.scalars(base, stream=92))
+    idx = (np.arange(n) * 2654435761 % base).astype(np.int64)
+    g1 = p1.reshape(base, G1)[idx].copy(); g2 = p2.reshape(base, G2)[(idx * 3 + 1) % base].copy()
+    if n >= 17:
+        g1[3] = util.G1_INF; g2[5] = util.G2_INF; g1[7], g2[7] = util.G1_GEN, util.G2_GEN
+    g1, g2 = g1.reshape(-1), g2.reshape(-1)
+    exp = c.pairing_many(g1, g2)
+    got = eng.pairing(g1, g2)
+    assert got.tobytes() == exp.tobytes()
+    ml, ok = eng.miller_loop_many(g2, g1)
+    rml, rok = c.miller_loop_many(g2, g1)
+    assert ml.tobytes() == rml.tobytes() and (ok == rok).all()
+    vals = ml.reshape(n, GT).copy()
+    if n >= 3:
+        vals[1] = 0                                                            # Option::None
+    fe, some = eng.final_exponentiation(vals.reshape(-1))
+    rfe, rsome = c.final_exp(vals.reshape(-1))
+    assert fe.tobytes() == rfe.tobytes() and (some == rsome).all()
+    if n % 3 == 0:
+        out, is_one = eng.pairing_batch(g1, g2, pairs_per_check=3)
+        rout, ris = c.pairing_product_many(g1, g2, 3)
+        assert out.tobytes() == rout.tobytes() and (is_one == ris).all()
+    e0 = bn.Engine(0, coop_max_n=0)                                            # the throughput kernels on the same inputs
+    try:
+        assert e0.pairing(g1, g2).tobytes() == got.tobytes()
+    finally:
+        e0.close()
+
+
+def test_golden_vector_on_the_latency_path(eng, golden):
+    """src/groups/mod.rs:928-999 at n = 1 is the warp-cooperative kernel's job; also n = 1 with the path disabled."""
+    import paritytech_bn_b200 as bn
+    v = golden["test_reduced_pairing"]
+    p = eng.g1_mul(util.G1_GEN, util.fr_bytes([int(v["g1_scalar"])]))
+    q = eng.g2_mul(util.G2_GEN, util.fr_bytes([int(v["g2_scalar"])]))
+    want = util.fq_mont_bytes([int(x) for x in v["expected"]])
+    assert eng.pairing(p, q).tobytes() == want
+    e0 = bn.Engine(0, coop_max_n=0)
+    try:
+        assert e0.pairing(p, q).tobytes() == want
+    finally:
+        e0.close()
+
+
 def test_conditional_subtraction_tie_cases(eng):
     """The predicated conditional subtraction decides on the top limb and takes a rare exact path when it ties
     with q's top limb: sums / differences / products landing in [q_top << 224, (q_top + 1) << 224)."""

@@ -4,11 +4,11 @@
 One WARP computes one pairing.  The warp is a 32-lane vector machine over Fq2: a per-warp file of Fq2 slots in shared memory
 and two instruction kinds, executed in lock step by all lanes, each lane with its own operands:
 
-  MUL  dst = conjA?(sum_{t<na} +-m_t slot[a_t])  *  conjB?(sum_{t<nb} +-m_t slot[b_t])          (one Fq2 product per lane)
+  MUL  dst = conjA?(sum_{t<na} +-slot[a_t])  *  conjB?(sum_{t<nb} +-slot[b_t])                  (one Fq2 product per lane)
   LIN  dst = half?( P + xi * X ),  P = sum of the terms of group 0, X = sum of the terms of group 1 (xi = 9 + u)
   INV  dst = (slot[a].c0)^-1 as (Fq, 0)   (one lane, Fermat in registers; everything else is MUL/LIN)
 
-m_t in {1, 2, 3}.  A routine is a short list of steps; a program is a list of calls (routine, base D, base A, base B): operand
+At most 8 terms per lane and step (na + nb, or |P| + |X|); small multiples are repeated terms.  A routine is a short list of steps; a program is a list of calls (routine, base D, base A, base B): operand
 addresses are absolute slots (sel 0) or relative to one of the three bases of the call (sel 1..3), so one MUL12 routine serves
 every Fq12 product of the final exponentiation.  The CUDA side is a generic executor with no knowledge of the algorithm;
 everything algorithmic lives here, where the simulator below runs the very same tables on Python integers against the oracle
@@ -64,30 +64,30 @@ def S(off):
 D, A, B = Ref(1, 0), Ref(2, 0), Ref(3, 0)
 
 
-def T(ref, sign=1, mult=1, grp=0):
-    """One term: +-mult * slot (group 1 = multiplied by xi in a LIN step)."""
-    assert sign in (1, -1) and mult in (1, 2, 3) and grp in (0, 1)
-    return (ref, sign, mult, grp)
+def T(ref, sign=1, grp=0):
+    """One term: +-slot (group 1 = multiplied by xi in a LIN step)."""
+    assert sign in (1, -1) and grp in (0, 1)
+    return (ref, sign, grp)
 
 
 def neg(t):
-    return (t[0], -t[1], t[2], t[3])
+    return (t[0], -t[1], t[2])
 
 
 def xi(t):
-    return (t[0], t[1], t[2], 1)
+    return (t[0], t[1], 1)
 
 
 def times(t, m):
-    assert t[2] * m <= 3
-    return (t[0], t[1], t[2] * m, t[3])
+    """m * t as repeated terms."""
+    return [t] * m
 
 
 def terms(x):
     """Normalise: a Ref, a term or a list of either -> list of terms."""
     if isinstance(x, Ref):
         return [T(x)]
-    if isinstance(x, tuple) and len(x) == 4 and isinstance(x[0], Ref):
+    if isinstance(x, tuple) and len(x) == 3 and isinstance(x[0], Ref):
         return [x]
     out = []
     for e in x:
@@ -102,17 +102,22 @@ class Step:
     def __init__(self, op):
         self.op, self.lanes = op, []      # lanes: dicts
 
-    def header(self):
+    def counts(self):
+        """(n0, n1): the uniform term counts of the step -- MUL: A side / B side, LIN: group 0 / group 1, INV: (1, 0)."""
         if self.op == OP_MUL:
-            na = max(len(l["a"]) for l in self.lanes)
-            nb = max(len(l["b"]) for l in self.lanes)
-            return self.op | (na << 4) | (nb << 8)
+            return max(len(l["a"]) for l in self.lanes), max(len(l["b"]) for l in self.lanes)
         if self.op == OP_LIN:
-            nt = max(len(l["t"]) for l in self.lanes)
-            has_xi = any(t[3] for l in self.lanes for t in l["t"])
-            has_half = any(l["half"] for l in self.lanes)
-            return self.op | (nt << 4) | (int(has_xi) << 12) | (int(has_half) << 13)
-        return self.op
+            return (max(sum(1 for t in l["t"] if t[2] == 0) for l in self.lanes),
+                    max(sum(1 for t in l["t"] if t[2] == 1) for l in self.lanes))
+        return 1, 0
+
+    def header(self):
+        """op | n0 << 4 | n1 << 8 | any conj << 12 | any half << 13"""
+        n0, n1 = self.counts()
+        assert n0 + n1 <= NT, (n0, n1)
+        cj = any(l.get("ca") or l.get("cb") for l in self.lanes)
+        hf = any(l.get("half") for l in self.lanes)
+        return self.op | (n0 << 4) | (n1 << 8) | (int(cj) << 12) | (int(hf) << 13)
 
 
 class Routine:
@@ -125,8 +130,8 @@ class Routine:
         for ln in lanes:
             dst, a, b = ln[0], terms(ln[1]), terms(ln[2])
             ca, cb = (ln[3], ln[4]) if len(ln) > 3 else (False, False)
-            assert 1 <= len(a) <= 4 and 1 <= len(b) <= 4, (self.name, len(a), len(b))
-            assert all(t[3] == 0 for t in a + b), "xi groups exist in LIN steps only"
+            assert 1 <= len(a) and 1 <= len(b), (self.name, len(a), len(b))
+            assert all(t[2] == 0 for t in a + b), "xi groups exist in LIN steps only"
             st.lanes.append(dict(dst=dst, a=a, b=b, ca=bool(ca), cb=bool(cb)))
         self._add(st)
 
@@ -136,6 +141,7 @@ class Routine:
         for ln in lanes:
             dst, t = ln[0], terms(ln[1])
             assert 1 <= len(t) <= NT, (self.name, len(t))
+            t = [x for x in t if x[2] == 0] + [x for x in t if x[2] == 1]          # group 0 first
             st.lanes.append(dict(dst=dst, t=t, half=bool(ln[2]) if len(ln) > 2 else False))
         self._add(st)
 
@@ -146,6 +152,7 @@ class Routine:
 
     def _add(self, st):
         assert 1 <= len(st.lanes) <= 32, (self.name, len(st.lanes))
+        st.header()                                                   # term budget
         # one synchronisation per step: no lane may read a slot that ANOTHER lane of the same step writes
         # (compared as (sel, off): two different bases may alias only where the call list says so -- checked by the simulator)
         for i, li in enumerate(st.lanes):
@@ -167,11 +174,10 @@ def _resolve(ref, bases):
 
 def _sum(slots, tl, bases, grp=None):
     acc = (0, 0)
-    for ref, sign, mult, g in tl:
+    for ref, sign, g in tl:
         if grp is not None and g != grp:
             continue
         v = slots[_resolve(ref, bases)]
-        v = ((v[0] * mult) % Q, (v[1] * mult) % Q)
         acc = o.fq2_add(acc, v) if sign > 0 else o.fq2_sub(acc, v)
     return acc
 
@@ -293,17 +299,16 @@ def build_routines():
 
     # ---- doubling step (src/groups/mod.rs:754-776): R in place, line into L
     r = new("DBL")
-    r.mul([(t_(0), RX, RY), (t_(1), RX, RX), (t_(2), RY, RY), (t_(3), RZ, RZ), (t_(4), [RY, RZ], [RY, RZ])])
+    r.mul([(t_(0), RX, RY), (LVV, [RX, RX, RX], RX), (t_(2), RY, RY), (t_(3), RZ, RZ), (t_(4), [RY, RZ], [RY, RZ])])   # ell_vv = 3 X^2
     r.lin([(t_(5), t_(0), True),                                                   # a = X Y / 2
            (t_(6), [T(t_(4)), T(t_(2), -1), T(t_(3), -1)]),                        # h = (Y + Z)^2 - b - c
-           (LVW, [T(t_(4), -1), T(t_(2)), T(t_(3))]),                              # ell_vw = -h
-           (LVV, T(t_(1), 1, 3))])                                                 # ell_vv = 3 X^2
+           (LVW, [T(t_(4), -1), T(t_(2)), T(t_(3))])])                             # ell_vw = -h
     r.mul([(t_(7), C_B3, t_(3))])                                                  # e = 3 b' Z^2
-    r.lin([(L0, [T(t_(7), 1, 1, 1), T(t_(2), -1, 1, 1)]),                          # ell_0 = xi (e - b)
-           (t_(8), [T(t_(2)), T(t_(7), 1, 3)], True),                              # g = (b + 3 e) / 2
-           (t_(9), [T(t_(2)), T(t_(7), -1, 3)])])                                  # b - f
-    r.mul([(RX, t_(5), t_(9)), (t_(10), t_(8), t_(8)), (t_(11), t_(7), t_(7)), (RZ, t_(2), t_(6))])
-    r.lin([(RY, [T(t_(10)), T(t_(11), -1, 3)])])                                   # Y' = g^2 - 3 e^2
+    r.lin([(L0, [T(t_(7), 1, 1), T(t_(2), -1, 1)]),                                # ell_0 = xi (e - b)
+           (t_(8), [T(t_(2))] + times(T(t_(7)), 3), True),                         # g = (b + 3 e) / 2
+           (t_(9), [T(t_(2))] + times(T(t_(7), -1), 3))])                          # b - f
+    r.mul([(RX, t_(5), t_(9)), (t_(10), t_(8), t_(8)), (t_(11), [t_(7), t_(7), t_(7)], t_(7)), (RZ, t_(2), t_(6))])
+    r.lin([(RY, [T(t_(10)), T(t_(11), -1)])])                                      # Y' = g^2 - 3 e^2
 
     # ---- mixed addition step (src/groups/mod.rs:731-752): R += the affine point at base B (x, y); line into L
     r = new("ADD")
@@ -313,9 +318,9 @@ def build_routines():
            (LVW, [T(RX), T(t_(0), -1)]), (LVV, [T(RY, -1), T(t_(1))])])             # ell_vw = d, ell_vv = -e
     r.mul([(t_(4), t_(2), t_(2)), (t_(5), t_(3), t_(3)), (t_(6), t_(3), bx), (t_(7), t_(2), by)])   # f, g, e x, d y
     r.mul([(t_(8), t_(2), t_(4)), (t_(9), RX, t_(4)), (t_(10), RZ, t_(5))])         # h, i, Z g
-    r.lin([(t_(11), [T(t_(10)), T(t_(8)), T(t_(9), -1, 2)]),                        # j = Z g + h - 2 i
-           (t_(12), [T(t_(9), 1, 3), T(t_(10), -1), T(t_(8), -1)]),                 # i - j
-           (L0, [T(t_(6), 1, 1, 1), T(t_(7), -1, 1, 1)])])                          # ell_0 = xi (e x - d y)
+    r.lin([(t_(11), [T(t_(10)), T(t_(8))] + times(T(t_(9), -1), 2)),                # j = Z g + h - 2 i
+           (t_(12), times(T(t_(9)), 3) + [T(t_(10), -1), T(t_(8), -1)]),            # i - j
+           (L0, [T(t_(6), 1, 1), T(t_(7), -1, 1)])])                                # ell_0 = xi (e x - d y)
     r.mul([(RX, t_(2), t_(11)), (t_(13), t_(3), t_(12)), (t_(14), t_(8), RY), (RZ, RZ, t_(8))])
     r.lin([(RY, [T(t_(13)), T(t_(14), -1)])])
 
@@ -369,16 +374,15 @@ def build_routines():
     a = [A + i for i in range(6)]
     pairs = [(a[0], a[4]), (a[3], a[2]), (a[1], a[5])]          # (z0, z1), (z2, z3), (z4, z5) in the reference's labels
     lanes = []
-    for k, (u, v) in enumerate(pairs):
-        lanes += [(t_(3 * k), u, u), (t_(3 * k + 1), v, v), (t_(3 * k + 2), [u, v], [u, v])]
+    for k, (u, v) in enumerate(pairs):           # 3 a^2, 3 b^2, 6 a b: the factors 3 and 2 ride on the operand sums
+        lanes += [(t_(3 * k), [u, u, u], u), (t_(3 * k + 1), [v, v, v], v), (t_(3 * k + 2), [u, u, u], [v, v])]
     r.mul(lanes)
 
     def t0(k, old):      # 3 (a^2 + xi b^2) - 2 old
-        return [T(t_(3 * k), 1, 3), T(old, -1, 2), T(t_(3 * k + 1), 1, 3, 1)]
+        return [T(t_(3 * k)), T(old, -1), T(old, -1), T(t_(3 * k + 1), 1, 1)]
 
-    def t1(k, old, with_xi):   # 3 (2ab) + 2 old, 2ab = (a + b)^2 - a^2 - b^2, times xi for the last pair
-        g = 1 if with_xi else 0
-        return [T(t_(3 * k + 2), 1, 3, g), T(t_(3 * k), -1, 3, g), T(t_(3 * k + 1), -1, 3, g), T(old, 1, 2)]
+    def t1(k, old, with_xi):   # 3 (2ab) + 2 old, times xi for the last pair
+        return [T(t_(3 * k + 2), 1, 1 if with_xi else 0), T(old), T(old)]
     r.lin([(D + 0, t0(0, a[0])), (D + 4, t1(0, a[4], False)),
            (D + 1, t0(1, a[1])), (D + 5, t1(1, a[5], False)),
            (D + 2, t0(2, a[2])), (D + 3, t1(2, a[3], True))])
@@ -572,3 +576,168 @@ def simulate_fexp(x):
     put_f12(slots, F.off, x)
     run_program(slots, R, calls[marks["fexp_begin"]:marks["fexp_end"]])
     return get_f12(slots, F.off)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# emitter: csrc/bn_coop_ucode.cuh
+# ------------------------------------------------------------------------------------------------------------------
+ZERO_TERM = 0        # slot 0 (the constant zero), plus sign
+
+
+def encode_term(t):
+    ref, sign, _ = t
+    return ref.code() | ((1 if sign < 0 else 0) << 10)
+
+
+def encode_step(st):
+    """header word and 5 x 32 lane words.  Lane word 0: dst | active << 10 | conjA << 11 | conjB << 12 | half << 13; words 1..4: eight
+    16-bit terms (slot code | minus << 10), first n0 terms = A side / group 0, next n1 = B side / group 1."""
+    n0, n1 = st.counts()
+    words = [[0] * 32 for _ in range(5)]
+    for lane in range(32):
+        if lane < len(st.lanes):
+            ln = st.lanes[lane]
+            if st.op == OP_MUL:
+                s0, s1 = ln["a"], ln["b"]
+            elif st.op == OP_LIN:
+                s0, s1 = [t for t in ln["t"] if t[2] == 0], [t for t in ln["t"] if t[2] == 1]
+            else:
+                s0, s1 = ln["t"], []
+            tl = [encode_term(t) for t in s0] + [ZERO_TERM] * (n0 - len(s0)) + [encode_term(t) for t in s1] + [ZERO_TERM] * (n1 - len(s1))
+            tl += [ZERO_TERM] * (NT - len(tl))
+            w0 = ln["dst"].code() | (1 << 10) | (int(ln.get("ca", False)) << 11) | (int(ln.get("cb", False)) << 12) | (int(ln.get("half", False)) << 13)
+        else:
+            tl, w0 = [ZERO_TERM] * NT, NO_DST
+        words[0][lane] = w0
+        for k in range(4):
+            words[1 + k][lane] = tl[2 * k] | (tl[2 * k + 1] << 16)
+    return st.header(), words
+
+
+def flatten():
+    """(steps, trace, marks): the distinct steps of all routines and the executed sequence (step index, bases) of the program."""
+    R = build_routines()
+    calls, marks = build_program()
+    index, steps = {}, []
+    for name, r in R.items():
+        for k, st in enumerate(r.steps):
+            index[(name, k)] = len(steps)
+            steps.append(st)
+    trace, tmarks, pos = [], {}, {}
+    for ci, (name, bd, ba, bb) in enumerate(calls):
+        pos[ci] = len(trace)
+        for k in range(len(R[name].steps)):
+            trace.append((index[(name, k)], bd, ba, bb))
+    pos[len(calls)] = len(trace)
+    for k, v in marks.items():
+        tmarks[k] = pos[v]
+    return steps, trace, tmarks
+
+
+def mont_limbs(v):
+    m = v * o.MONT_R % Q
+    return [(m >> (32 * i)) & 0xffffffff for i in range(8)]
+
+
+def emit(path):
+    steps, trace, marks = flatten()
+    out = []
+    w = out.append
+    w("// GENERATED by tools/gen_coop_ucode.py -- do not edit.  Microcode of the warp-cooperative pairing (csrc/bn_coop.cuh):")
+    w("// %d distinct steps, %d executed steps per pairing.  The simulator in the generator runs these very tables against the oracle." % (len(steps), len(trace)))
+    w("#pragma once")
+    w("#include <stdint.h>")
+    w("#define BN_COOP_NSLOTS %d" % ((N_SLOTS + 1) & ~1))
+    w("#define BN_COOP_NSTEPS %d" % len(steps))
+    w("#define BN_COOP_NTRACE %d" % len(trace))
+    w("#define BN_COOP_NCONST %d" % N_CONST)
+    w("#define BN_COOP_SLOT_IN_P %d" % IN_P.off)
+    w("#define BN_COOP_SLOT_IN_Q %d" % IN_Q.off)
+    w("#define BN_COOP_SLOT_F %d" % F.off)
+    for k in ("pairing_begin", "miller_end", "fexp_begin", "fexp_end", "pairing_end"):
+        w("#define BN_COOP_T_%s %d" % (k.upper(), marks[k]))
+    hdrs, code = [], []
+    for st in steps:
+        h, words = encode_step(st)
+        hdrs.append(h)
+        for k in range(5):
+            code.extend(words[k])
+
+    def arr(name, vals, per=12):
+        w("__device__ const uint32_t %s[%d] = {" % (name, len(vals)))
+        for i in range(0, len(vals), per):
+            w("    " + ", ".join("0x%08xu" % v for v in vals[i:i + per]) + ",")
+        w("};")
+    arr("bn_coop_hdr", hdrs)
+    arr("bn_coop_code", code, 16)
+    arr("bn_coop_trace", [s | (bd << 8) | (ba << 16) | (bb << 24) for s, bd, ba, bb in trace])
+    cs = constants()
+    vals = []
+    for k in range(N_CONST):
+        c = cs.get(k, (0, 0))
+        vals += mont_limbs(c[0]) + mont_limbs(c[1])
+    arr("bn_coop_const", vals, 8)
+    assert len(steps) < 256
+    open(path, "w").write("\n".join(out) + "\n")
+    return len(steps), len(trace)
+
+
+def decode_and_run(p, q):
+    """Simulate from the ENCODED tables (what the GPU executes): decodes bn_coop words back into terms."""
+    steps, trace, marks = flatten()
+    enc = [encode_step(st) for st in steps]
+    slots = fresh_slots()
+    for i in range(3):
+        slots[IN_P.off + i] = (p[i] % Q, 0)
+        slots[IN_Q.off + i] = q[i]
+    half_inv = pow(2, -1, Q)
+    for s, bd, ba, bb in trace[marks["pairing_begin"]:marks["pairing_end"]]:
+        h, words = enc[s]
+        op, n0, n1 = h & 15, (h >> 4) & 15, (h >> 8) & 15
+        bases = (0, bd, ba, bb)
+        writes = []
+        for lane in range(32):
+            w0 = words[0][lane]
+            if not (w0 >> 10) & 1:
+                continue
+            tl = []
+            for k in range(4):
+                tl += [words[1 + k][lane] & 0xffff, words[1 + k][lane] >> 16]
+
+            def acc(ts):
+                a = (0, 0)
+                for t in ts:
+                    v = slots[(t & 0xff) + bases[(t >> 8) & 3]]
+                    a = o.fq2_sub(a, v) if (t >> 10) & 1 else o.fq2_add(a, v)
+                return a
+            x, y = acc(tl[:n0]), acc(tl[n0:n0 + n1])
+            if op == OP_MUL:
+                if (w0 >> 11) & 1:
+                    x = _conj(x)
+                if (w0 >> 12) & 1:
+                    y = _conj(y)
+                r = o.fq2_mul(x, y)
+            elif op == OP_LIN:
+                r = o.fq2_add(x, o.fq2_mul_by_nonresidue(y))
+                if (w0 >> 13) & 1:
+                    r = (r[0] * half_inv % Q, r[1] * half_inv % Q)
+            else:
+                r = (pow(x[0], Q - 2, Q), 0)
+            writes.append(((w0 & 0xff) + bases[(w0 >> 8) & 3], r))
+        for d, r in writes:
+            slots[d] = r
+    return get_f12(slots, F.off)
+
+
+if __name__ == "__main__":
+    import random
+    if "--check" in sys.argv:
+        rng = random.Random(1)
+        for _ in range(3):
+            p = o.g_mul(o.FQ_OPS, o.G1_ONE, rng.randrange(1, o.R_ORDER))
+            q = o.g_mul(o.FQ2_OPS, o.G2_ONE, rng.randrange(1, o.R_ORDER))
+            assert simulate(p, q) == o.pairing(p, q) == decode_and_run(p, q)
+        print("microcode matches the oracle")
+    else:
+        n = emit(os.path.join(ROOT, "paritytech-bn_b200", "csrc", "bn_coop_ucode.cuh"))
+        print("wrote bn_coop_ucode.cuh: %d steps, %d executed per pairing" % n)
