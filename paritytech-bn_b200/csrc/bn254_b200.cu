@@ -252,6 +252,7 @@ static int ctx_init(bn254_ctx* c, int device, const bn254_ctx_options* user) {
         CU(cudaFuncSetAttribute(k_final_exp_hard_sync, cudaFuncAttributeMaxDynamicSharedMemorySize, smem7));
     }
     CU(cudaFuncSetAttribute(k_coop_pairing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BN_COOP_SMEM(BN_COOP_MAX_WARPS)));
+    CU(cudaFuncSetAttribute(k_coop_gt_pow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BN_COOP_SMEM(BN_COOP_MAX_WARPS)));
     // the main stream outranks the second one: in the pipelined path the first half batch gets ahead of the second
     int prio_least = 0, prio_greatest = 0;
     cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
@@ -911,6 +912,13 @@ int bn254_gt_pow_many(bn254_ctx* ctx, const void* a, const void* fr, void* out, 
     ENTER(ctx);
     if (n && (!a || !fr || !out)) return fail(BN254_ERR_ARG, "null pointer");
     return gt_host(ctx, a, fr, sizeof(Fq), out, nullptr, n, [&](const Lane& L, void** d) -> int {
+        if (use_coop(ctx, n)) {   // small batches: one warp per element (k_coop_gt_pow)
+            size_t per_sm = (n + (size_t)ctx->sms - 1) / (size_t)ctx->sms;
+            unsigned warps = per_sm > BN_COOP_MAX_WARPS ? (unsigned)BN_COOP_MAX_WARPS : (unsigned)per_sm;
+            unsigned g = (unsigned)((n + warps - 1) / warps);
+            LAUNCH_SYNC(L, k_coop_gt_pow, g, warps * 32, BN_COOP_SMEM(warps), (const Fq12*)d[0], (const Fq*)d[1], (Fq12*)d[2], n);
+            return 0;
+        }
         LAUNCH(L, k_gt_pow, n, (const Fq12*)d[0], (const Fq*)d[1], (Fq12*)d[2], n);
         return 0;
     });

@@ -96,22 +96,32 @@ __device__ __forceinline__ void coop_step(uint32_t tr, sp s_code, sp s_hdr, sp w
     }
 }
 
+// the tables travel to shared memory once per block (46 KB): every step then decodes from on-chip memory
+__device__ __forceinline__ sp coop_load_tables() {
+    uint32_t* dst = reinterpret_cast<uint32_t*>(bn_slot_mem);
+    for (unsigned k = threadIdx.x; k < BN_COOP_CODE_WORDS; k += blockDim.x) dst[k] = bn_coop_code[k];
+    for (unsigned k = threadIdx.x; k < BN_COOP_NSTEPS; k += blockDim.x) dst[BN_COOP_CODE_WORDS + k] = bn_coop_hdr[k];
+    for (unsigned k = threadIdx.x; k < BN_COOP_NTRACE; k += blockDim.x) dst[BN_COOP_CODE_WORDS + BN_COOP_NSTEPS + k] = bn_coop_trace[k];
+    __syncthreads();
+    return (sp)__cvta_generic_to_shared(bn_slot_mem);
+}
+// run the `count` steps of one routine starting at step `begin` with the bases (D, A, B) packed as D << 8 | A << 16 | B << 24
+__device__ __forceinline__ void coop_call(unsigned begin, unsigned count, uint32_t bases, sp s_code, sp s_hdr, sp wbase, unsigned lane) {
+#pragma unroll 1
+    for (unsigned k = 0; k < count; k++) {
+        coop_step((begin + k) | bases, s_code, s_hdr, wbase, lane);
+        __syncwarp();
+    }
+}
+
 // mode 0: out[i] = pairing(g1[i], g2[i]) (one for a pair with a point at infinity, src/groups/mod.rs:896)
 // mode 1: out[i] = the un-exponentiated Miller value of the pair (one, ok[i] = 0 at infinity)
 // mode 2: out[i] = final_exponentiation(in[i]), in passed through g1_or_gt (may alias out); ok[i] = 0 and zero for in == 0 (None)
 // out, ok, is_one may each be null; is_one[i] = (result == Gt::one()).
 __global__ void __launch_bounds__(BN_COOP_MAX_WARPS * 32, 1) k_coop_pairing(const void* g1_or_gt, const G2* __restrict__ g2, Fq12* out,
                                                                             uint8_t* __restrict__ ok, uint8_t* __restrict__ is_one, size_t n, int mode) {
-    const sp tab = (sp)__cvta_generic_to_shared(bn_slot_mem);
+    const sp tab = coop_load_tables();
     const sp s_code = tab, s_hdr = tab + 4u * BN_COOP_CODE_WORDS, s_trace = s_hdr + 4u * BN_COOP_NSTEPS;
-    // the tables travel to shared memory once per block (46 KB): every step then decodes from on-chip memory
-    {
-        uint32_t* dst = reinterpret_cast<uint32_t*>(bn_slot_mem);
-        for (unsigned k = threadIdx.x; k < BN_COOP_CODE_WORDS; k += blockDim.x) dst[k] = bn_coop_code[k];
-        for (unsigned k = threadIdx.x; k < BN_COOP_NSTEPS; k += blockDim.x) dst[BN_COOP_CODE_WORDS + k] = bn_coop_hdr[k];
-        for (unsigned k = threadIdx.x; k < BN_COOP_NTRACE; k += blockDim.x) dst[BN_COOP_CODE_WORDS + BN_COOP_NSTEPS + k] = bn_coop_trace[k];
-    }
-    __syncthreads();
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const size_t i = (size_t)blockIdx.x * (blockDim.x >> 5) + warp;
     if (i >= n) return;                                          // whole warps leave: nothing below synchronises the block
@@ -170,6 +180,50 @@ __global__ void __launch_bounds__(BN_COOP_MAX_WARPS * 32, 1) k_coop_pairing(cons
     const bool all_same = __all_sync(0xffffffffu, same);
     if (is_one && lane == 0) is_one[i] = all_same ? 1 : 0;
     if (ok && lane == 0) ok[i] = good ? 1 : 0;
+}
+
+// Gt::pow (src/lib.rs:592 -> FieldElement::pow, src/fields/mod.rs:35-46) one warp per element: MSB-first square-and-multiply over
+// the canonical scalar with the SQR12 / MUL12 routines of the microcode (accumulator in the F slots, base in register 1);
+// leading zero bits only square one, so skipping them gives the same value (as fq12_pow of bn_tower.cuh does).
+__global__ void __launch_bounds__(BN_COOP_MAX_WARPS * 32, 1) k_coop_gt_pow(const Fq12* __restrict__ a, const Fq* __restrict__ fr,
+                                                                           Fq12* __restrict__ out, size_t n) {
+    const sp tab = coop_load_tables();
+    const sp s_code = tab, s_hdr = tab + 4u * BN_COOP_CODE_WORDS;
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const size_t i = (size_t)blockIdx.x * (blockDim.x >> 5) + warp;
+    if (i >= n) return;
+    const sp wbase = tab + 4u * BN_COOP_TABLE_WORDS + warp * BN_COOP_SLOT_BYTES;
+    for (unsigned k = lane; k < BN_COOP_NCONST * 16u; k += 32u) sts32(wbase + 4u * k, bn_coop_const[k]);
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(a + i);
+    for (unsigned k = lane; k < 96u; k += 32u) sts32(wbase + 64u * BN_COOP_SLOT_EREG1 + 4u * k, src[k]);
+    Fq m = fr[i];
+    uint32_t e[8];
+    fr_to_canonical(e, m.v);                                     // every lane the same scalar: the walk below is uniform
+    // F = one
+    {
+        const Fq one = fq_one();
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (lane == 0) v = make_uint4(one.v[0], one.v[1], one.v[2], one.v[3]);
+        if (lane == 1) v = make_uint4(one.v[4], one.v[5], one.v[6], one.v[7]);
+        if (lane < 24u) sts128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane, v);
+    }
+    __syncwarp();
+    bool started = false;
+    const uint32_t mul_bases = ((uint32_t)BN_COOP_SLOT_F << 8) | ((uint32_t)BN_COOP_SLOT_F << 16) | ((uint32_t)BN_COOP_SLOT_EREG1 << 24);
+#pragma unroll 1
+    for (int b = 255; b >= 0; b--) {
+        if (started) coop_call(BN_COOP_R_SQR12_BEGIN, BN_COOP_R_SQR12_COUNT, 0u, s_code, s_hdr, wbase, lane);
+        if ((e[b >> 5] >> (b & 31)) & 1u) {
+            if (started) {
+                coop_call(BN_COOP_R_MUL12_BEGIN, BN_COOP_R_MUL12_COUNT, mul_bases, s_code, s_hdr, wbase, lane);
+            } else {
+                if (lane < 24u) sts128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane, lds128(wbase + 64u * BN_COOP_SLOT_EREG1 + 16u * lane));
+                __syncwarp();
+                started = true;
+            }
+        }
+    }
+    if (lane < 24u) reinterpret_cast<uint4*>(out + i)[lane] = lds128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane);
 }
 
 }  // namespace bn

@@ -35,6 +35,14 @@ def test_final_exponentiation_phase_alone():
     assert g.simulate_fexp(f) == o.fq12_final_exponentiation(f)
 
 
+def test_pow_walk_with_in_place_routines():
+    """SQR12 on the accumulator and MUL12 with D aliasing A, as k_coop_gt_pow calls them (Gt::pow, src/lib.rs:592)."""
+    p, q = _pair()
+    a = g.simulate(p, q)
+    for k in (0, 1, 2, 0xb5, rng.randrange(1 << 70)):
+        assert g.simulate_pow(a, k) == o.fq12_pow(a, k)
+
+
 def test_encoded_tables_decode_to_the_same_result():
     """What is emitted (16-bit terms, lane words, headers, trace) is what was simulated."""
     p, q = _pair()

@@ -424,6 +424,10 @@ def test_warp_cooperative_latency_path(eng, n):
     fe, some = eng.final_exponentiation(vals.reshape(-1))
     rfe, rsome = c.final_exp(vals.reshape(-1))
     assert fe.tobytes() == rfe.tobytes() and (some == rsome).all()
+    # Gt::pow one warp per element: edge scalars 0, 1, 2, r-1 next to random ones
+    ks = ([0, 1, 2, o.R_ORDER - 1] + util.scalars(n, stream=93))[:n]
+    pw = eng.gt_pow(got, util.fr_bytes(ks))
+    assert pw.tobytes() == c.gt_pow(got, util.fr_bytes(ks)).tobytes()
     if n % 3 == 0:
         out, is_one = eng.pairing_batch(g1, g2, pairs_per_check=3)
         rout, ris = c.pairing_product_many(g1, g2, 3)

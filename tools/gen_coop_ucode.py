@@ -569,6 +569,26 @@ def simulate(p, q, phase="pairing"):
     return get_f12(slots, F.off)
 
 
+def simulate_pow(a, k):
+    """Gt::pow the way k_coop_gt_pow walks it: MSB first, SQR12 on the accumulator in F, MUL12 (D = A = F, B = the base in
+    register 1) on set bits; leading zero bits skipped (FieldElement::pow squares one there: same value)."""
+    R = build_routines()
+    slots = fresh_slots()
+    put_f12(slots, ereg(1), a)
+    put_f12(slots, F.off, o.FQ12_ONE)
+    started = False
+    for i in range(255, -1, -1):
+        if started:
+            run_program(slots, R, [("SQR12", 0, 0, 0)])
+        if (k >> i) & 1:
+            if started:
+                run_program(slots, R, [("MUL12", F.off, F.off, ereg(1))])
+            else:
+                put_f12(slots, F.off, a)
+                started = True
+    return get_f12(slots, F.off)
+
+
 def simulate_fexp(x):
     R = build_routines()
     calls, marks = build_program()
@@ -656,6 +676,15 @@ def emit(path):
     w("#define BN_COOP_SLOT_F %d" % F.off)
     for k in ("pairing_begin", "miller_end", "fexp_begin", "fexp_end", "pairing_end"):
         w("#define BN_COOP_T_%s %d" % (k.upper(), marks[k]))
+    # step ranges of the routines a kernel may call on its own (Gt::pow walks its scalar with SQR12 / MUL12)
+    R = build_routines()
+    pos = 0
+    for name, r in R.items():
+        if name in ("SQR12", "MUL12"):
+            w("#define BN_COOP_R_%s_BEGIN %d" % (name, pos))
+            w("#define BN_COOP_R_%s_COUNT %d" % (name, len(r.steps)))
+        pos += len(r.steps)
+    w("#define BN_COOP_SLOT_EREG1 %d" % ereg(1))
     hdrs, code = [], []
     for st in steps:
         h, words = encode_step(st)
