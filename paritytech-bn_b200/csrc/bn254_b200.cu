@@ -1470,3 +1470,44 @@ extern "C" int bn254_final_exp_many_dev_noalloc(bn254_ctx* ctx, const void* d_gt
     return 0;
     API_END
 }
+
+#ifdef BN_SLOT_CHECK
+// ---------------------------------------------------------------------------------------------
+// Test build only (-DBN_SLOT_CHECK, libbn254_b200_chk.so): read-out of the shared-memory ownership / bounds checker of
+// bn_slots.cuh, and a negative control that proves it is live.  Not declared in include/bn254_b200.h.
+// ---------------------------------------------------------------------------------------------
+namespace bn {
+// thread 5 writes the first word of thread 6's slots through the checked accessor: exactly one violation, nothing stored
+__global__ void k_slot_check_poke() {
+    const sp base = s_base();
+    if (threadIdx.x == 5) sts128(base + BN_SLOT_STRIDE, make_uint4(1, 2, 3, 4));
+}
+}  // namespace bn
+extern "C" int bn254_debug_slot_violations(bn254_ctx* ctx, unsigned long long* out4) {
+    API_BEGIN
+    ENTER(ctx);
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream2));
+    CU(cudaMemcpyFromSymbol(out4, bn_slot_violations, 4 * sizeof(unsigned long long)));
+    return 0;
+    API_END
+}
+extern "C" int bn254_debug_slot_reset(bn254_ctx* ctx) {
+    API_BEGIN
+    ENTER(ctx);
+    unsigned long long z[4] = {0, 0, 0, 0};
+    CU(cudaStreamSynchronize(ctx->stream));
+    CU(cudaMemcpyToSymbol(bn_slot_violations, z, sizeof z));
+    return 0;
+    API_END
+}
+extern "C" int bn254_debug_slot_poke(bn254_ctx* ctx) {
+    API_BEGIN
+    ENTER(ctx);
+    Lane L = main_lane(ctx);
+    LAUNCH_SYNC(L, k_slot_check_poke, 1, BN_BLOCK, BN_BLOCK * BN_SLOT_STRIDE);
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+    API_END
+}
+#endif

@@ -171,7 +171,11 @@ __global__ void __launch_bounds__(BN_SYNC_MAX_BLOCK, 1) k_final_exp_hard_sync(co
         for (int row = 0; row < 24; row++) {
             unsigned g = row * 32u + lane;                           // 16-byte word of the warp's 12 KB
             unsigned t = g / 24u, w = g - t * 24u;
-            if (first + t < n) o[g] = lds128(wbase + t * stride + 16 * w);
+            if (first + t < n) {
+                const sp src = wbase + t * stride + 16 * w;          // another lane's slots: the warp's 32 regions
+                BN_SLOT_GUARD(slot_ok(2u, src, 16u, wbase, 32u * stride)) continue;
+                o[g] = lds128_raw(src);
+            }
         }
     }
     if (!live) return;

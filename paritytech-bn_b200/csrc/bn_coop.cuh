@@ -29,16 +29,53 @@ namespace bn {
 #define BN_COOP_SMEM(warps) ((size_t)BN_COOP_TABLE_WORDS * 4 + (size_t)(warps) * BN_COOP_SLOT_BYTES)
 #define BN_COOP_DEFAULT_MAX_N 2368                             /* up to one warp per pairing on every SM (148 x 16) */
 
+// Accessors of the cooperative kernels.  Reads may touch the block's read-only tables or the warp's own slot file, writes only
+// the warp's own file (checked in -DBN_SLOT_CHECK builds, bn_slots.cuh).
+#ifdef BN_SLOT_CHECK
+__device__ __forceinline__ bool coop_ok(sp a, unsigned bytes, bool write) {
+    const sp dyn0 = (sp)__cvta_generic_to_shared(bn_slot_mem);
+    const sp file = dyn0 + 4u * BN_COOP_TABLE_WORDS + (threadIdx.x >> 5) * BN_COOP_SLOT_BYTES;
+    if (!write && a < dyn0 + 4u * BN_COOP_TABLE_WORDS) return slot_ok(3u, a, bytes, dyn0, 4u * BN_COOP_TABLE_WORDS);
+    return slot_ok(write ? 5u : 4u, a, bytes, file, BN_COOP_SLOT_BYTES);
+}
+#endif
 __device__ __forceinline__ uint32_t lds32(sp a) {
-    uint32_t v;
+    uint32_t v = 0;
+    BN_SLOT_GUARD(coop_ok(a, 4u, false)) return v;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a) : "memory");
     return v;
 }
-__device__ __forceinline__ void sts32(sp a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ void sts32(sp a, uint32_t v) {
+    BN_SLOT_GUARD(coop_ok(a, 4u, true)) return;
+    asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint4 c_lds128(sp a) {
+    BN_SLOT_GUARD(coop_ok(a, 16u, false)) return make_uint4(0, 0, 0, 0);
+    return lds128_raw(a);
+}
+__device__ __forceinline__ void c_sts128(sp a, uint4 v) {
+    BN_SLOT_GUARD(coop_ok(a, 16u, true)) return;
+    sts128_raw(a, v);
+}
+__device__ __forceinline__ Fq2 c_ld(sp a) {
+    uint4 w0 = c_lds128(a), w1 = c_lds128(a + 16), w2 = c_lds128(a + 32), w3 = c_lds128(a + 48);
+    Fq2 r;
+    r.c0.v[0] = w0.x; r.c0.v[1] = w0.y; r.c0.v[2] = w0.z; r.c0.v[3] = w0.w;
+    r.c0.v[4] = w1.x; r.c0.v[5] = w1.y; r.c0.v[6] = w1.z; r.c0.v[7] = w1.w;
+    r.c1.v[0] = w2.x; r.c1.v[1] = w2.y; r.c1.v[2] = w2.z; r.c1.v[3] = w2.w;
+    r.c1.v[4] = w3.x; r.c1.v[5] = w3.y; r.c1.v[6] = w3.z; r.c1.v[7] = w3.w;
+    return r;
+}
+__device__ __forceinline__ void c_st(sp a, const Fq2& v) {
+    c_sts128(a, make_uint4(v.c0.v[0], v.c0.v[1], v.c0.v[2], v.c0.v[3]));
+    c_sts128(a + 16, make_uint4(v.c0.v[4], v.c0.v[5], v.c0.v[6], v.c0.v[7]));
+    c_sts128(a + 32, make_uint4(v.c1.v[0], v.c1.v[1], v.c1.v[2], v.c1.v[3]));
+    c_sts128(a + 48, make_uint4(v.c1.v[4], v.c1.v[5], v.c1.v[6], v.c1.v[7]));
+}
 // acc +- slot named by the 16-bit term t (slot code | minus << 10); bases: byte k = base of selector k (byte 0 = 0)
 __device__ __forceinline__ void coop_acc(Fq2& acc, uint32_t t, sp wbase, uint32_t bases) {
     const uint32_t slot = (t & 0xffu) + ((bases >> (8u * ((t >> 8) & 3u))) & 0xffu);
-    const Fq2 x = s_ld(wbase + slot * 64u);
+    const Fq2 x = c_ld(wbase + slot * 64u);
     if (t & 0x400u) { fq_sub(acc.c0, acc.c0, x.c0); fq_sub(acc.c1, acc.c1, x.c1); }
     else { fq_add(acc.c0, acc.c0, x.c0); fq_add(acc.c1, acc.c1, x.c1); }
 }
@@ -92,7 +129,7 @@ __device__ __forceinline__ void coop_step(uint32_t tr, sp s_code, sp s_hdr, sp w
     }
     if (active) {
         const uint32_t slot = (w0 & 0xffu) + ((bases >> (8u * ((w0 >> 8) & 3u))) & 0xffu);
-        s_st(wbase + slot * 64u, r);
+        c_st(wbase + slot * 64u, r);
     }
 }
 
@@ -173,7 +210,7 @@ __global__ void __launch_bounds__(BN_COOP_MAX_WARPS * 32, 1) k_coop_pairing(cons
     if (lane == 0) one_w = make_uint4(one.v[0], one.v[1], one.v[2], one.v[3]);
     if (lane == 1) one_w = make_uint4(one.v[4], one.v[5], one.v[6], one.v[7]);
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (good) { if (lane < 24u) v = lds128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane); }
+    if (good) { if (lane < 24u) v = c_lds128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane); }
     else if (mode != 2) v = one_w;                               // infinity -> one; a zero input of mode 2 -> zero
     if (out && lane < 24u) reinterpret_cast<uint4*>(out + i)[lane] = v;          // 384 contiguous bytes per warp
     const bool same = lane >= 24u || (v.x == one_w.x && v.y == one_w.y && v.z == one_w.z && v.w == one_w.w);
@@ -205,7 +242,7 @@ __global__ void __launch_bounds__(BN_COOP_MAX_WARPS * 32, 1) k_coop_gt_pow(const
         uint4 v = make_uint4(0, 0, 0, 0);
         if (lane == 0) v = make_uint4(one.v[0], one.v[1], one.v[2], one.v[3]);
         if (lane == 1) v = make_uint4(one.v[4], one.v[5], one.v[6], one.v[7]);
-        if (lane < 24u) sts128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane, v);
+        if (lane < 24u) c_sts128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane, v);
     }
     __syncwarp();
     bool started = false;
@@ -217,13 +254,13 @@ __global__ void __launch_bounds__(BN_COOP_MAX_WARPS * 32, 1) k_coop_gt_pow(const
             if (started) {
                 coop_call(BN_COOP_R_MUL12_BEGIN, BN_COOP_R_MUL12_COUNT, mul_bases, s_code, s_hdr, wbase, lane);
             } else {
-                if (lane < 24u) sts128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane, lds128(wbase + 64u * BN_COOP_SLOT_EREG1 + 16u * lane));
+                if (lane < 24u) c_sts128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane, c_lds128(wbase + 64u * BN_COOP_SLOT_EREG1 + 16u * lane));
                 __syncwarp();
                 started = true;
             }
         }
     }
-    if (lane < 24u) reinterpret_cast<uint4*>(out + i)[lane] = lds128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane);
+    if (lane < 24u) reinterpret_cast<uint4*>(out + i)[lane] = c_lds128(wbase + 64u * BN_COOP_SLOT_F + 16u * lane);
 }
 
 }  // namespace bn

@@ -28,13 +28,55 @@ namespace bn {
 #define BN_SLOT_BLOCK7 448              /* largest block with 7 slots per thread */
 typedef uint32_t sp;   // shared-window byte address of one Fq2 slot
 
-__device__ __forceinline__ uint4 lds128(sp a) {
+__device__ __forceinline__ uint4 lds128_raw(sp a) {
     uint4 v;
     asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a) : "memory");
     return v;
 }
-__device__ __forceinline__ void sts128(sp a, uint4 v) {
+__device__ __forceinline__ void sts128_raw(sp a, uint4 v) {
     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" :: "r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+extern __shared__ uint4 bn_slot_mem[];
+// -DBN_SLOT_CHECK (test build `libbn254_b200_chk.so`, scripts/slot_check_cases.py): every shared-memory access of the slot-file
+// and warp-cooperative kernels is checked against the region its issuer owns -- the thread's own slots (stride rule of s_base),
+// the warp's 32 slot regions in the coalesced result epilogue, the warp's file plus the read-only tables in bn_coop.cuh -- and
+// against the block's dynamic shared memory size and the access alignment.  A violation is counted in a device global and the
+// access is skipped.  compute-sanitizer is closed on this pool; this is the stand-in for its memcheck, and since every thread
+// (warp) then provably touches only memory it owns between barriers, also for racecheck.
+#ifdef BN_SLOT_CHECK
+__device__ unsigned long long bn_slot_violations[4];   // [0] count, [1] first offending address | kind << 32, [2] blockIdx, [3] threadIdx | blockDim << 32
+__device__ __noinline__ void slot_violation(unsigned kind, sp a) {
+    if (atomicAdd(&bn_slot_violations[0], 1ull) == 0ull) {
+        bn_slot_violations[1] = (unsigned long long)a | ((unsigned long long)kind << 32);
+        bn_slot_violations[2] = blockIdx.x;
+        bn_slot_violations[3] = threadIdx.x | ((unsigned long long)blockDim.x << 32);
+    }
+}
+// [lo, lo + len) must contain [a, a + bytes), inside the block's dynamic shared memory, naturally aligned
+__device__ __forceinline__ bool slot_ok(unsigned kind, sp a, unsigned bytes, sp lo, unsigned len) {
+    const sp dyn0 = (sp)__cvta_generic_to_shared(bn_slot_mem);
+    unsigned dyn_size;
+    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(dyn_size));
+    const bool ok = (a & (bytes - 1u)) == 0u && a >= lo && a + bytes <= lo + len && lo >= dyn0 && lo + len <= dyn0 + dyn_size;
+    if (!ok) slot_violation(kind, a);
+    return ok;
+}
+__device__ __forceinline__ bool slot_ok_own(sp a, unsigned bytes) {
+    const unsigned stride = blockDim.x > 448 ? (6 * 64 + 16) : (7 * 64 + 16);
+    return slot_ok(1u, a, bytes, (sp)__cvta_generic_to_shared(bn_slot_mem) + threadIdx.x * stride, stride);
+}
+#define BN_SLOT_GUARD(cond) if (!(cond)) 
+#else
+#define BN_SLOT_GUARD(cond) if (false)
+#endif
+// accessors of the slot-file kernels: the calling thread's own slots
+__device__ __forceinline__ uint4 lds128(sp a) {
+    BN_SLOT_GUARD(slot_ok_own(a, 16u)) return make_uint4(0, 0, 0, 0);
+    return lds128_raw(a);
+}
+__device__ __forceinline__ void sts128(sp a, uint4 v) {
+    BN_SLOT_GUARD(slot_ok_own(a, 16u)) return;
+    sts128_raw(a, v);
 }
 __device__ __forceinline__ Fq2 s_ld(sp a) {
     uint4 w0 = lds128(a), w1 = lds128(a + 16), w2 = lds128(a + 32), w3 = lds128(a + 48);
@@ -51,7 +93,6 @@ __device__ __forceinline__ void s_st(sp a, const Fq2& v) {
     sts128(a + 32, make_uint4(v.c1.v[0], v.c1.v[1], v.c1.v[2], v.c1.v[3]));
     sts128(a + 48, make_uint4(v.c1.v[4], v.c1.v[5], v.c1.v[6], v.c1.v[7]));
 }
-extern __shared__ uint4 bn_slot_mem[];
 __device__ __forceinline__ sp s_base() {
     const unsigned stride = blockDim.x > BN_SLOT_BLOCK7 ? BN_SLOT_STRIDE6 : BN_SLOT_STRIDE;
     return (sp)__cvta_generic_to_shared(bn_slot_mem) + threadIdx.x * stride;

@@ -454,6 +454,24 @@ def test_golden_vector_on_the_latency_path(eng, golden):
         e0.close()
 
 
+def test_shared_memory_ownership_check_build():
+    """compute-sanitizer is closed on this pool; its stand-in is the -DBN_SLOT_CHECK build, whose slot accessors verify that
+    every shared-memory access of the slot-file and warp-cooperative kernels stays inside the region its issuer owns.
+    scripts/slot_check_cases.py runs the small cases of every such kernel on it (results vs the oracle), expects 0 violations,
+    and exactly 1 after a deliberate out-of-region store (the checker is live)."""
+    import subprocess
+    import sys
+
+    import paritytech_bn_b200 as bn
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if not os.path.exists(bn.library_path("_chk")):
+        import __graft_entry__
+        __graft_entry__.build()
+    p = subprocess.run([sys.executable, os.path.join(root, "scripts", "slot_check_cases.py")], capture_output=True, text=True, timeout=1200)
+    assert p.returncode == 0, p.stdout[-3000:] + p.stderr[-3000:]
+    assert "slot check ok: 0 violations" in p.stdout
+
+
 def test_conditional_subtraction_tie_cases(eng):
     """The predicated conditional subtraction decides on the top limb and takes a rare exact path when it ties
     with q's top limb: sums / differences / products landing in [q_top << 224, (q_top + 1) << 224)."""
