@@ -181,6 +181,19 @@ int bn254_g2_mul_normalized_many_dev(bn254_ctx* ctx, const void* d_g2, const voi
 int bn254_g1_normalize_many(bn254_ctx* ctx, const void* g1, void* g1_out, size_t n);
 int bn254_g2_normalize_many(bn254_ctx* ctx, const void* g2, void* g2_out, size_t n);
 
+/* ---- the group law itself, elementwise: src/lib.rs:405-423, :556-574 (Add, Sub via Neg, Neg), Group::double, derived ==
+ * -> src/groups/mod.rs:294-334 (add-2007-bl with the zero / equal-point branches), :250-269 (dbl-2009-l), :336-350 (Neg),
+ * :169-195 (PartialEq: PROJECTIVE equality, eq[i] = 1 when both triples name the same point).  Results are the reference's own
+ * Jacobian representatives (same formulas), so raw bytes match. */
+int bn254_g1_add_many(bn254_ctx* ctx, const void* a, const void* b, void* out, size_t n);
+int bn254_g2_add_many(bn254_ctx* ctx, const void* a, const void* b, void* out, size_t n);
+int bn254_g1_double_many(bn254_ctx* ctx, const void* a, void* out, size_t n);
+int bn254_g2_double_many(bn254_ctx* ctx, const void* a, void* out, size_t n);
+int bn254_g1_neg_many(bn254_ctx* ctx, const void* a, void* out, size_t n);
+int bn254_g2_neg_many(bn254_ctx* ctx, const void* a, void* out, size_t n);
+int bn254_g1_eq_many(bn254_ctx* ctx, const void* a, const void* b, uint8_t* eq, size_t n);
+int bn254_g2_eq_many(bn254_ctx* ctx, const void* a, const void* b, uint8_t* eq, size_t n);
+
 /* ---- AffineG1::new / AffineG2::new: src/lib.rs:437-447, :639-649 -> src/groups/mod.rs:94-113 ---- */
 /* xy: n affine points (x, y) as Montgomery images (64 B for G1, 128 B for G2).  status[i] = 0 Ok,
  * 1 GroupError::NotOnCurve, 2 GroupError::NotInSubgroup (G2 only: p * (-1) + p != 0). */

@@ -317,6 +317,46 @@ class Engine:
         self._check(self.lib.bn254_g2_mul_normalized_many(self.ctx, _p(g2), _p(fr), _p(out), ctypes.c_size_t(n)))
         return out
 
+    def _group_op(self, which, op, a, b=None):
+        unit = G1_BYTES if which == "g1" else G2_BYTES
+        a, n = _arr(a, unit)
+        fn = getattr(self.lib, "bn254_%s_%s_many" % (which, op))
+        if op in ("add", "eq"):
+            b, n2 = _arr(b, unit)
+            assert n == n2
+            out = np.empty(n if op == "eq" else n * unit, dtype=np.uint8)
+            self._check(fn(self.ctx, _p(a), _p(b), _p(out), ctypes.c_size_t(n)))
+        else:
+            out = np.empty(n * unit, dtype=np.uint8)
+            self._check(fn(self.ctx, _p(a), _p(out), ctypes.c_size_t(n)))
+        return out
+
+    def g1_add(self, a, b):
+        """G1 + G1 elementwise (src/lib.rs:405-411): the reference's Jacobian representative."""
+        return self._group_op("g1", "add", a, b)
+
+    def g2_add(self, a, b):
+        return self._group_op("g2", "add", a, b)
+
+    def g1_double(self, a):
+        return self._group_op("g1", "double", a)
+
+    def g2_double(self, a):
+        return self._group_op("g2", "double", a)
+
+    def g1_neg(self, a):
+        return self._group_op("g1", "neg", a)
+
+    def g2_neg(self, a):
+        return self._group_op("g2", "neg", a)
+
+    def g1_eq(self, a, b):
+        """G1 == G1 elementwise: projective equality (src/groups/mod.rs:169-195), one byte per element."""
+        return self._group_op("g1", "eq", a, b)
+
+    def g2_eq(self, a, b):
+        return self._group_op("g2", "eq", a, b)
+
     def g1_normalize(self, g1):
         g1, n = _arr(g1, G1_BYTES)
         out = np.empty(n * G1_BYTES, dtype=np.uint8)

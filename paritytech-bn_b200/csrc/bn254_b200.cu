@@ -1053,6 +1053,39 @@ static int normalize_host(bn254_ctx* ctx, const void* p, void* out, size_t n) {
     return 0;
 }
 
+// host-pointer wrapper of the elementwise group operations (k_jac_elementwise): op 0 add, 1 double, 2 neg, 3 eq
+template <class P, class F>
+static int group_op_host(bn254_ctx* ctx, int op, const void* a, const void* b, void* out, uint8_t* eq, size_t n) {
+    if (n == 0) return 0;
+    const bool binary = op == 0 || op == 3;
+    if (!a || (binary && !b) || (op == 3 ? !eq : !out)) return fail(BN254_ERR_ARG, "null pointer");
+    size_t sz[4] = {n * sizeof(P), binary ? n * sizeof(P) : 0, op == 3 ? 0 : n * sizeof(P), op == 3 ? n : 0};
+    void* d[4];
+    TRY(ctx_io(ctx, sz, 4, d));
+    Lane L = main_lane(ctx);
+    TRY(h2d(L, d[0], a, sz[0]));
+    if (binary) TRY(h2d(L, d[1], b, sz[1]));
+    LAUNCH(L, k_jac_elementwise<F>, n, op, (const P*)d[0], (const P*)d[1], (P*)d[2], (uint8_t*)d[3], n);
+    if (op == 3) TRY(d2h(L, eq, d[3], n)); else TRY(d2h(L, out, d[2], sz[2]));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+#define GROUP_OP_API(name, P, F, op, A, B, OUT, EQ)                                   \
+    API_BEGIN                                                                         \
+    ENTER(ctx);                                                                       \
+    return group_op_host<P, F>(ctx, op, A, B, OUT, EQ, n);                            \
+    API_END
+extern "C" {
+int bn254_g1_add_many(bn254_ctx* ctx, const void* a, const void* b, void* out, size_t n) { GROUP_OP_API(add, G1, FqOps, 0, a, b, out, nullptr) }
+int bn254_g2_add_many(bn254_ctx* ctx, const void* a, const void* b, void* out, size_t n) { GROUP_OP_API(add, G2, Fq2Ops, 0, a, b, out, nullptr) }
+int bn254_g1_double_many(bn254_ctx* ctx, const void* a, void* out, size_t n) { GROUP_OP_API(dbl, G1, FqOps, 1, a, nullptr, out, nullptr) }
+int bn254_g2_double_many(bn254_ctx* ctx, const void* a, void* out, size_t n) { GROUP_OP_API(dbl, G2, Fq2Ops, 1, a, nullptr, out, nullptr) }
+int bn254_g1_neg_many(bn254_ctx* ctx, const void* a, void* out, size_t n) { GROUP_OP_API(neg, G1, FqOps, 2, a, nullptr, out, nullptr) }
+int bn254_g2_neg_many(bn254_ctx* ctx, const void* a, void* out, size_t n) { GROUP_OP_API(neg, G2, Fq2Ops, 2, a, nullptr, out, nullptr) }
+int bn254_g1_eq_many(bn254_ctx* ctx, const void* a, const void* b, uint8_t* eq, size_t n) { GROUP_OP_API(eq, G1, FqOps, 3, a, b, nullptr, eq) }
+int bn254_g2_eq_many(bn254_ctx* ctx, const void* a, const void* b, uint8_t* eq, size_t n) { GROUP_OP_API(eq, G2, Fq2Ops, 3, a, b, nullptr, eq) }
+}  // extern "C"
+
 static int affine_check_dev(bn254_ctx* ctx, const void* d_xy, uint8_t* d_status, size_t n, bool g2) {
     if (n == 0) return 0;
     if (!d_xy || !d_status) return fail(BN254_ERR_ARG, "null pointer");

@@ -594,6 +594,19 @@ BN_KERNEL k_jac_mul(const Jac<F>* __restrict__ p, const Fq* __restrict__ fr, Jac
     jac_mul(r, x, k);
     out[i] = r;
 }
+// Elementwise group operations (src/groups/mod.rs:250-269 double, :294-334 Add, :336-350 Neg, :169-195 PartialEq):
+// op 0 = a + b, 1 = 2 a, 2 = -a, 3 = (a == b) as one byte per element
+template <class F>
+BN_KERNEL k_jac_elementwise(int op, const Jac<F>* __restrict__ a, const Jac<F>* __restrict__ b, Jac<F>* __restrict__ out,
+                            uint8_t* __restrict__ eq, size_t n) {
+    size_t i = gtid();
+    if (i >= n) return;
+    Jac<F> x = a[i], r;
+    if (op == 0) { Jac<F> y = b[i]; jac_add(r, x, y); out[i] = r; }
+    else if (op == 1) { jac_double(r, x); out[i] = r; }
+    else if (op == 2) { jac_neg(r, x); out[i] = r; }
+    else { Jac<F> y = b[i]; eq[i] = jac_eq(x, y) ? 1 : 0; }
+}
 // (p * k).normalize() by the signed 4-bit window (jac_mul_normalized, bn_curve.cuh); the 8-entry table lives in local memory
 template <class F>
 BN_KERNEL k_jac_mul_window(const Jac<F>* __restrict__ p, const Fq* __restrict__ fr, Jac<F>* __restrict__ out, size_t n) {

@@ -90,6 +90,27 @@ template <class F> BN_HD_NOINLINE void jac_add(Jac<F>& r, const Jac<F>& p, const
     r.x = x3;
     F::mul(r.z, zz, h);
 }
+// Neg, src/groups/mod.rs:336-350: (x, -y, z); the point at infinity is returned unchanged
+template <class F> BN_HD void jac_neg(Jac<F>& r, const Jac<F>& p) {
+    r = p;
+    if (!F::is_zero(p.z)) F::neg(r.y, p.y);
+}
+// PartialEq, src/groups/mod.rs:169-195: projective equality x1 z2^2 == x2 z1^2 and y1 z2^3 == y2 z1^3; infinity only equals infinity
+template <class F> BN_HD bool jac_eq(const Jac<F>& p, const Jac<F>& o) {
+    if (F::is_zero(p.z)) return F::is_zero(o.z);
+    if (F::is_zero(o.z)) return false;
+    typename F::T z1s, z2s, a, b;
+    F::sqr(z1s, p.z);
+    F::sqr(z2s, o.z);
+    F::mul(a, p.x, z2s);
+    F::mul(b, o.x, z1s);
+    if (!F::eq(a, b)) return false;
+    F::mul(z1s, p.z, z1s);
+    F::mul(z2s, o.z, z2s);
+    F::mul(a, p.y, z2s);
+    F::mul(b, o.y, z1s);
+    return F::eq(a, b);
+}
 // G * Fr, src/groups/mod.rs:272-292: MSB-first double-and-add over the canonical (de-Montgomeryed)
 // scalar bits, exactly the reference's sequence, so even the raw Jacobian triple matches.
 template <class F> BN_HD void jac_mul(Jac<F>& r, const Jac<F>& p, const uint32_t (&k)[8]) {

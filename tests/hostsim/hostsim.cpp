@@ -29,6 +29,13 @@ UN(fq12_final_exp_last_chunk, Fq12, fq12_final_exp_last_chunk)
 BIN(g1_add, G1, jac_add) BIN(g2_add, G2, jac_add) UN(g1_double, G1, jac_double) UN(g2_double, G2, jac_double)
 UN(g1_normalize, G1, jac_normalize) UN(g2_normalize, G2, jac_normalize)
 
+UN(g1_neg, G1, jac_neg) UN(g2_neg, G2, jac_neg)
+extern "C" void hs_g1_eq(const void* a, const void* b, unsigned char* eq, size_t n) {
+    for (size_t i = 0; i < n; i++) { G1 x = ld<G1>(a, i), y = ld<G1>(b, i); eq[i] = jac_eq(x, y); }
+}
+extern "C" void hs_g2_eq(const void* a, const void* b, unsigned char* eq, size_t n) {
+    for (size_t i = 0; i < n; i++) { G2 x = ld<G2>(a, i), y = ld<G2>(b, i); eq[i] = jac_eq(x, y); }
+}
 extern "C" void hs_fq_inv(const void* a, void* o, unsigned char* some, size_t n) {
     for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r; some[i] = fq_inv(r, x); st(o, i, r); }
 }

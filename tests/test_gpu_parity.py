@@ -241,6 +241,38 @@ def test_scalar_mul_config4_sizes(eng, which, log2n):
     assert raw[:m2 * unit].tobytes() == cmul(base[:m2 * unit], fr[:m2 * FR]).tobytes()  # the reference's own Jacobian representative
 
 
+def test_group_law_elementwise(eng):
+    """bn254_g{1,2}_{add,double,neg,eq}_many: the reference's own Jacobian representatives (raw bytes vs the C oracle for add /
+    double, vs the Python oracle for neg and ==), with the zero / equal-point branches of add, infinity, and == across different
+    representatives of one point."""
+    n = 300
+    p, q = _workload(n, 15)
+    p2, q2 = _workload(n, 16)
+    P, Q, P2, Q2 = (x.reshape(n, -1).copy() for x in (p, q, p2, q2))
+    P2[0], Q2[0] = P[0], Q[0]                                # equal points: the doubling branch of add
+    P[1], Q[1] = util.G1_INF, util.G2_INF                    # infinity + b = b
+    P2[2], Q2[2] = util.G1_INF, util.G2_INF                  # a + infinity = a
+    P2[3], Q2[3] = eng.g1_neg(P[3]), eng.g2_neg(Q[3])        # a + (-a) = infinity
+    a1, a2, b1, b2 = P.reshape(-1), Q.reshape(-1), P2.reshape(-1), Q2.reshape(-1)
+    s1, s2 = eng.g1_add(a1, b1), eng.g2_add(a2, b2)
+    assert s1.tobytes() == c.g1_add(a1, b1).tobytes() and s2.tobytes() == c.g2_add(a2, b2).tobytes()
+    assert not s1.reshape(n, G1)[3][64:].any() and not s2.reshape(n, G2)[3][128:].any()      # z == 0
+    assert eng.g1_double(a1).tobytes() == c.g1_double(a1).tobytes() and eng.g2_double(a2).tobytes() == c.g2_double(a2).tobytes()
+    m = 40
+    for which, a, unit, F, frm in (("g1", a1, G1, o.FQ_OPS, o.g1_from_bytes), ("g2", a2, G2, o.FQ2_OPS, o.g2_from_bytes)):
+        neg = getattr(eng, which + "_neg")(a)
+        pts = [frm(a[i * unit:(i + 1) * unit].tobytes()) for i in range(m)]
+        assert neg[:m * unit].tobytes() == b"".join(o.to_bytes(o.g_neg(F, x)) for x in pts)
+        norm = getattr(eng, which + "_normalize")(a)
+        eq = getattr(eng, which + "_eq")
+        assert eq(a, norm).all()                                             # same points, other representatives
+        assert eq(getattr(eng, which + "_add")(a, a), getattr(eng, which + "_double")(a)).all()
+        shifted = np.roll(a.reshape(n, unit), 1, axis=0).reshape(-1)
+        want = [int(o.g_eq(F, x, frm(shifted[i * unit:(i + 1) * unit].tobytes()))) for i, x in enumerate(pts)]
+        assert list(eq(a, shifted)[:m]) == want and not any(want[2:])
+        assert eq(getattr(eng, which + "_add")(a, neg), np.tile(util.G1_INF if which == "g1" else util.G2_INF, n)).all()
+
+
 def test_gt_algebra_and_joux(eng):
     """Gt::{mul,pow,inverse,==} and the Joux three-party check of examples/joux.rs:7-21."""
     a, b, cc = util.scalars(3, stream=21)

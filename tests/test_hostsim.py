@@ -140,6 +140,42 @@ def test_groups_and_scalar_mul():
     assert out.tobytes() == c.g2_mul(q, fr).tobytes()
 
 
+def _group_cases():
+    """(a, b, expected ==) over G1 and G2: equal points in different Jacobian representatives, different points, negatives,
+    infinity against infinity (any (x, y, 0)) and against a finite point."""
+    p, q = _points(6)
+    n = p.size // G1
+    P, Q = p.reshape(n, G1).copy(), q.reshape(n, G2).copy()
+    pn, qn = c.g1_normalize(p).reshape(n, G1), c.g2_normalize(q).reshape(n, G2)
+    inf1 = np.frombuffer(o.to_bytes((0, 1, 0)), dtype=np.uint8)
+    inf1b = np.frombuffer(o.to_bytes((5, 7, 0)), dtype=np.uint8)
+    inf2 = np.frombuffer(o.to_bytes(((0, 0), (1, 0), (0, 0))), dtype=np.uint8)
+    a1 = np.stack([P[0], P[1], P[2], inf1, inf1, P[3]])
+    b1 = np.stack([pn[0], P[2], pn[2], inf1b, P[4], inf1])
+    a2 = np.stack([Q[0], Q[1], Q[2], inf2, inf2, Q[3]])
+    b2 = np.stack([qn[0], Q[2], qn[2], inf2, Q[4], inf2])
+    return a1.reshape(-1), b1.reshape(-1), a2.reshape(-1), b2.reshape(-1), [1, 0, 1, 1, 0, 0]
+
+
+def test_group_neg_and_projective_equality_host_build():
+    """jac_neg / jac_eq (src/groups/mod.rs:336-350, :169-195) of the device headers against the Python oracle."""
+    a1, b1, a2, b2, want = _group_cases()
+    n = len(want)
+    for name, a, b, unit, F, frm in (("g1", a1, b1, G1, o.FQ_OPS, o.g1_from_bytes), ("g2", a2, b2, G2, o.FQ2_OPS, o.g2_from_bytes)):
+        eq = np.empty(n, dtype=np.uint8)
+        getattr(hostsim.lib(), "hs_%s_eq" % name)(_p(a), _p(b), _p(eq), ctypes.c_size_t(n))
+        pts_a = [frm(a[i * unit:(i + 1) * unit].tobytes()) for i in range(n)]
+        pts_b = [frm(b[i * unit:(i + 1) * unit].tobytes()) for i in range(n)]
+        assert list(eq) == [int(o.g_eq(F, x, y)) for x, y in zip(pts_a, pts_b)] == want
+        neg = hs_un("%s_neg" % name, a, unit)
+        assert neg.tobytes() == b"".join(o.to_bytes(o.g_neg(F, x)) for x in pts_a)
+        # p + (-p) is the point at infinity, and == says so
+        add = hs_bin("%s_add" % name, a, neg, unit)
+        inf = np.tile(np.frombuffer(o.to_bytes(o.g_zero(F)), dtype=np.uint8), n)
+        getattr(hostsim.lib(), "hs_%s_eq" % name)(_p(add), _p(inf), _p(eq), ctypes.c_size_t(n))
+        assert eq.all()
+
+
 def test_window_scalar_mul_normalized_host_build():
     """jac_mul_normalized (signed 4-bit window, the body of k_jac_mul_window) == the oracle's (p * k).normalize(), bytes and
     all: random scalars, the edge scalars 0 / 1 / 2 / r-1, scalars made of extreme digits (8s, 9s -> -7 with carries, 0xf...),
