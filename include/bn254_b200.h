@@ -17,7 +17,9 @@
  * Every entry point is batched (pointer + count); the scalar functions of src/lib.rs are the n = 1
  * calls.  Host-pointer entry points are synchronous: they stage through the context's grow-only device
  * arenas (no cudaMalloc on the steady-state path) and return when the results are in the caller's
- * buffers.  `*_dev` entry points take DEVICE pointers (16-byte aligned, checked: BN254_ERR_ARG otherwise)
+ * buffers.  Host buffers may be pageable, page-locked, or page-locked in part (a cudaHostRegister of a sub-range: copies are
+ * split at the boundary, and the zero-copy result path is taken only when the whole output extent is mapped).
+ * `*_dev` entry points take DEVICE pointers (16-byte aligned, checked: BN254_ERR_ARG otherwise)
  * and enqueue on the context's stream.  They do not synchronise, with two documented exceptions:
  *   - the first call that needs a larger workspace than any call before it grows the arena
  *     (cudaStreamSynchronize + cudaFree + cudaMalloc, once);

@@ -135,14 +135,28 @@ static void* mapped_device_ptr(const void* host, size_t bytes) {
     if (b.type != cudaMemoryTypeHost || (char*)b.devicePointer != (char*)a.devicePointer + (bytes - 1)) return nullptr;
     return a.devicePointer;
 }
-static int h2d(const Lane& L, void* d, const void* h, size_t bytes) {
-    if (bytes) CU(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, L.stream));
-    return 0;
+// Host <-> device copies.  CUDA refuses ONE copy whose host range is partly page-locked (cudaHostRegister of a part of the
+// buffer) and partly pageable with cudaErrorInvalidValue; such a range is split in halves until every piece lies on one side of
+// the registration boundary, which CUDA tracks to the byte (cuts are page aligned while the piece is larger than a page; at most
+// ~log2(bytes) refused calls).
+static int copy_split(const Lane& L, char* dst, const char* src, size_t bytes, cudaMemcpyKind kind) {
+    if (bytes == 0) return 0;
+    cudaError_t e = cudaMemcpyAsync(dst, src, bytes, kind, L.stream);
+    if (e == cudaSuccess) return 0;
+    if (e != cudaErrorInvalidValue || bytes <= 1) return fail(BN254_ERR_CUDA, "cudaMemcpyAsync", e);
+    cudaGetLastError();
+    const char* host = kind == cudaMemcpyHostToDevice ? src : dst;
+    size_t half = bytes / 2;
+    size_t cut = half;
+    if (bytes > 8192) {   // the first piece ends on a page boundary
+        cut = (((uintptr_t)host + half + 4095) & ~(uintptr_t)4095) - (uintptr_t)host;
+        if (cut == 0 || cut >= bytes) cut = half;
+    }
+    TRY(copy_split(L, dst, src, cut, kind));
+    return copy_split(L, dst + cut, src + cut, bytes - cut, kind);
 }
-static int d2h(const Lane& L, void* h, const void* d, size_t bytes) {
-    if (bytes) CU(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, L.stream));
-    return 0;
-}
+static int h2d(const Lane& L, void* d, const void* h, size_t bytes) { return copy_split(L, (char*)d, (const char*)h, bytes, cudaMemcpyHostToDevice); }
+static int d2h(const Lane& L, void* h, const void* d, size_t bytes) { return copy_split(L, (char*)h, (const char*)d, bytes, cudaMemcpyDeviceToHost); }
 // grow-only arena: a larger request than any before synchronises the context's streams once and reallocates
 static int arena_reserve(bn254_ctx* ctx, Arena& a, size_t bytes, const char* what) {
     if (bytes <= a.bytes) return 0;
