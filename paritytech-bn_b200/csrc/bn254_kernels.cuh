@@ -43,7 +43,7 @@ __device__ __noinline__ bool pair_to_affine(AffG1& pa, AffG2& qa, const G1& p, c
     fq_mul(t, q.z.c1, q.z.c1);
     fq_add(n, n, t);                 // norm(q.z) != 0
     fq_mul_ni(t, p.z, n);
-    fq_inv_w4(ti, t);
+    fq_inv_eea(ti, t);                // binary extended Euclid: a third of the Fermat power's pipe time, same element
     fq_mul_ni(pzi, ti, n);           // 1/p.z
     fq_mul_ni(ni, ti, p.z);          // 1/norm
     fq_mul_ni(z2, pzi, pzi);
@@ -676,7 +676,11 @@ BN_KERNEL k_field_op(int op, const uint4* __restrict__ a, const uint4* __restric
     switch (op) {
         case 0: case 1: case 2: case 9: {
             Fq x = reinterpret_cast<const Fq*>(a)[i], r;
-            if (op == 9) { fq_inv(r, x); }
+            if (op == 9) {   // both inversions must agree: Fermat power and the uniform binary extended Euclid (all-ones if not)
+                Fq r2, r3;
+                fq_inv(r, x); fq_inv_eea(r2, x); fq_inv_w4(r3, x);
+                if (!fq_eq(r, r2) || !fq_eq(r, r3)) { for (int k = 0; k < 8; k++) r.v[k] = 0xffffffffu; }
+            }
             else {
                 Fq y = reinterpret_cast<const Fq*>(b)[i];
                 if (op == 0) fq_mul(r, x, y); else if (op == 1) fq_add(r, x, y); else fq_sub(r, x, y);

@@ -6,7 +6,7 @@
 // BN_COOP_NSLOTS Fq2 slots in shared memory, and two instruction kinds executed in lock step, every lane with its own operands
 //     MUL  dst = conjA?(sum +-slot[a_t]) * conjB?(sum +-slot[b_t])        one Fq2 product per lane
 //     LIN  dst = half?(P + xi X)                                          P, X = signed sums of slots
-// plus INV (one lane, Fermat inversion in registers).  The 18 Fq2 products of an Fq12 multiplication, the 12 of a squaring,
+// plus INV (one lane, binary extended Euclid in registers).  The 18 Fq2 products of an Fq12 multiplication, the 12 of a squaring,
 // the 9 of a cyclotomic squaring, the 18 of a line multiplication and the products of a G2 line step run on as many lanes
 // at once; the dependent chain shrinks from 17,730 Fq multiplications to 1,651 steps.
 //
@@ -125,7 +125,7 @@ __device__ __forceinline__ void coop_step(uint32_t tr, sp s_code, sp s_hdr, sp w
         }
     } else {                                                     // INV: one lane
         r.c0 = fq_zero(); r.c1 = fq_zero();
-        if (active) fq_inv_w4(r.c0, x.c0);
+        if (active) fq_inv_eea(r.c0, x.c0);
     }
     if (active) {
         const uint32_t slot = (w0 & 0xffu) + ((bases >> (8u * ((w0 >> 8) & 3u))) & 0xffu);

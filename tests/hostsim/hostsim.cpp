@@ -39,6 +39,9 @@ extern "C" void hs_g2_eq(const void* a, const void* b, unsigned char* eq, size_t
 extern "C" void hs_fq_inv(const void* a, void* o, unsigned char* some, size_t n) {
     for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r; some[i] = fq_inv(r, x); st(o, i, r); }
 }
+extern "C" void hs_fq_inv_eea(const void* a, void* o, unsigned char* some, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r; some[i] = fq_inv_eea(r, x); st(o, i, r); }
+}
 extern "C" void hs_fq_inv_w4(const void* a, void* o, unsigned char* some, size_t n) {
     for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r; some[i] = fq_inv_w4(r, x); st(o, i, r); }
 }

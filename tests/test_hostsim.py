@@ -72,9 +72,23 @@ def test_inversions_and_frobenius():
     out = np.empty_like(a)
     some = np.empty(40, dtype=np.uint8)
     ro, rs = c.fq_inv(a)
-    for fn in ("hs_fq_inv", "hs_fq_inv_w4"):               # binary ladder and the 4-bit window used by pair_to_affine
+    for fn in ("hs_fq_inv", "hs_fq_inv_w4", "hs_fq_inv_eea"):     # Fermat ladder, its 4-bit window, the uniform binary extended Euclid
         getattr(hostsim.lib(), fn)(_p(a), _p(out), _p(some), ctypes.c_size_t(40))
         assert (some == rs).all() and out.tobytes() == ro.tobytes()
+    # the Euclid loop at its extremes: 1, 2, q - 1, q - 2, powers of two (long runs of halvings), values next to q / 2, the
+    # Montgomery one and R^2; plus 2,000 random residues
+    vals = [1, 2, 3, o.Q - 1, o.Q - 2, (o.Q - 1) // 2, (o.Q + 1) // 2, o.MONT_R % o.Q, (o.MONT_R * o.MONT_R) % o.Q, 0]
+    vals += [(1 << k) % o.Q for k in (1, 31, 32, 63, 64, 127, 128, 253, 254, 255)] + [o.Q - (1 << k) for k in (1, 32, 200, 253)]
+    vals += [rng.randrange(o.Q) for _ in range(2000)]
+    a = np.frombuffer(b"".join(v.to_bytes(32, "little") for v in vals), dtype=np.uint8).copy()      # raw Montgomery images
+    out, some = np.empty_like(a), np.empty(len(vals), dtype=np.uint8)
+    hostsim.lib().hs_fq_inv_eea(_p(a), _p(out), _p(some), ctypes.c_size_t(len(vals)))
+    for i, v in enumerate(vals):
+        got = int.from_bytes(out[32 * i:32 * i + 32].tobytes(), "little")
+        if v == 0:
+            assert some[i] == 0 and got == 0
+        else:       # image v = a R  ->  image of the inverse = a^-1 R = R^2 / v
+            assert some[i] == 1 and got == pow(v, -1, o.Q) * o.MONT_R * o.MONT_R % o.Q, i
     a = np.concatenate([rand_elems(12, 6), _b(o.FQ12_ZERO)])
     out = np.empty_like(a)
     some = np.empty(7, dtype=np.uint8)
