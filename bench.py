@@ -195,6 +195,20 @@ def main():
         reference_arm(args, rank, world)
         return 0
 
+    # Under torchrun every rank gets its own slice of the host cores BEFORE torch / CUDA start their threads, so that the ranks'
+    # copy and launch threads do not migrate over one another (recorded in config.cpu_affinity; BN254_BENCH_PIN=0 disables).
+    affinity = None
+    if world > 1 and os.environ.get("BN254_BENCH_PIN", "1") != "0" and hasattr(os, "sched_setaffinity"):
+        try:
+            cores_all = sorted(os.sched_getaffinity(0))
+            per = len(cores_all) // world
+            if per >= 1:
+                mine = cores_all[local * per:(local + 1) * per]
+                os.sched_setaffinity(0, mine)
+                affinity = "%d-%d of %d host cores per rank" % (mine[0], mine[-1], len(cores_all))
+        except OSError:
+            affinity = None
+
     import torch
     import torch.distributed as dist
 
@@ -395,7 +409,7 @@ def main():
             "vs_baseline": None, "dtype": "u32 limbs (256-bit Montgomery, mod q)", "data": "synthetic",
             "config": {"workload": "2^%d independent BN254 pairings per GPU (BASELINE configs[1]), random Jacobian points z != 1" % args.batch_log2,
                        "batch_per_gpu": n, "l2": "flushed between steps (256 MiB write)", "library": eng.build_info(),
-                       "source_sha16": source_sha16(), "parity_checked_pairings": parity_n},
+                       "source_sha16": source_sha16(), "parity_checked_pairings": parity_n, "cpu_affinity": affinity},
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": "pairings/s", "h2d_bytes_per_step": n * (G1 + G2), "d2h_bytes_per_step": n * GT,
                     "api": "Engine.pairing -> bn254_pairing_many (pinned host buffers)", "ms_per_step": e2e_s * 1e3},
