@@ -88,6 +88,9 @@ typedef struct bn254_ctx_options {
                               (one warp per pairing); 0 disables it */
     int32_t stack_bytes;   /* BN254_STACK_BYTES   0: leave cudaLimitStackSize alone (the driver sizes static call graphs itself);
                               > 0: raise the DEVICE-WIDE limit to at least this (affects the embedding process) */
+    int32_t mul_compact;   /* BN254_MUL_COMPACT   1: G1 * Fr (reference sequence) compacts a block's additions onto full warps
+                              (k_jac_mul_compact, +6 %); 2: G2 * Fr as well (no gain, tests); 0: one thread per scalar with its
+                              own `if (bit) add` (k_jac_mul).  Same Jacobian bytes in every mode. */
 } bn254_ctx_options;
 void bn254_ctx_options_default(bn254_ctx_options* opt);
 int bn254_ctx_create(int device, bn254_ctx** out);

@@ -607,6 +607,102 @@ BN_KERNEL k_jac_elementwise(int op, const Jac<F>* __restrict__ a, const Jac<F>* 
     else if (op == 2) { jac_neg(r, x); out[i] = r; }
     else { Jac<F> y = b[i]; eq[i] = jac_eq(x, y) ? 1 : 0; }
 }
+// G * Fr on the reference's exact add/double sequence (src/groups/mod.rs:272-292; raw Jacobian bytes match), with the additions
+// of a BLOCK compacted onto full warps.  k_jac_mul above gives every thread its own `if (bit) add`: with 32 independent scalars in
+// a warp the addition runs for almost every bit with half the lanes idle (0.54 of the IMAD peak, DESIGN F16).  Here the block's
+// running points and bases live in shared memory; per bit every thread doubles its own point, the threads whose bit is set
+// append their index to a list (ballot + prefix sum), and the first `count` threads of the block perform the additions of the
+// listed items -- about half the warps take the addition, fully occupied, the others skip it.  Each item still sees exactly the
+// reference's sequence (double, then add when its bit is set), so the result is the same Jacobian triple.
+#define BN_CMUL_BLOCK 256
+template <class F> struct CmulLayout {
+    static constexpr unsigned PT = sizeof(Jac<F>);              // 96 (G1) / 192 (G2)
+    static constexpr unsigned STRIDE = 2 * PT + 16;              // res + base, odd number of 16-byte units: conflict-free per-thread access
+    static constexpr unsigned LIST = BN_CMUL_BLOCK * STRIDE;     // uint32 list[BN_CMUL_BLOCK]
+    static constexpr unsigned COUNTS = LIST + 4 * BN_CMUL_BLOCK; // uint32 warp_count[8] + total
+    static constexpr unsigned BYTES = COUNTS + 64;
+};
+template <class F> __device__ __forceinline__ void cmul_load(Jac<F>& d, sp a) {
+    uint4* w = reinterpret_cast<uint4*>(&d);
+#pragma unroll
+    for (unsigned k = 0; k < sizeof(Jac<F>) / 16; k++) w[k] = lds128_raw(a + 16 * k);
+}
+template <class F> __device__ __forceinline__ void cmul_store(sp a, const Jac<F>& v) {
+    const uint4* w = reinterpret_cast<const uint4*>(&v);
+#pragma unroll
+    for (unsigned k = 0; k < sizeof(Jac<F>) / 16; k++) sts128_raw(a + 16 * k, w[k]);
+}
+template <class F>
+__global__ void __launch_bounds__(BN_CMUL_BLOCK, 2) k_jac_mul_compact(const Jac<F>* __restrict__ p, const Fq* __restrict__ fr,
+                                                                      Jac<F>* __restrict__ out, size_t n) {
+    typedef CmulLayout<F> LY;
+    const sp base = (sp)__cvta_generic_to_shared(bn_slot_mem);
+    const unsigned tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    const size_t i = (size_t)blockIdx.x * BN_CMUL_BLOCK + tid;
+    const bool live = i < n;
+    uint32_t k[8];
+    {
+        Jac<F> x, z;
+        jac_set_zero(z);
+        if (live) {
+            x = p[i];
+            Fq m = fr[i];
+            fr_to_canonical(k, m.v);
+        } else {
+            x = z;
+#pragma unroll
+            for (int j = 0; j < 8; j++) k[j] = 0;
+        }
+        cmul_store<F>(base + tid * LY::STRIDE, z);                  // running point: zero
+        cmul_store<F>(base + tid * LY::STRIDE + LY::PT, x);         // base point
+    }
+    bool found_one = false;
+    __syncthreads();
+#pragma unroll 1
+    for (int b = 255; b >= 0; b--) {
+        const bool bit = (k[b >> 5] >> (b & 31)) & 1u;
+        // every thread doubles its own running point (the reference doubles only after the first set bit)
+        if (found_one) {
+            Jac<F> r;
+            cmul_load<F>(r, base + tid * LY::STRIDE);
+            jac_double(r, r);
+            cmul_store<F>(base + tid * LY::STRIDE, r);
+        }
+        found_one = found_one || bit;
+        // list of the items whose bit is set
+        const unsigned mask = __ballot_sync(0xffffffffu, bit);
+        if (lane == 0) asm volatile("st.shared.u32 [%0], %1;" :: "r"(base + LY::COUNTS + 4u * warp), "r"(__popc(mask)) : "memory");
+        __syncthreads();                                           // doublings stored, warp counts visible
+        unsigned before = 0, total = 0;
+#pragma unroll
+        for (unsigned w = 0; w < BN_CMUL_BLOCK / 32; w++) {
+            unsigned c;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c) : "r"(base + LY::COUNTS + 4u * w) : "memory");
+            before += w < warp ? c : 0u;
+            total += c;
+        }
+        if (bit) {
+            const unsigned pos = before + __popc(mask & ((1u << lane) - 1u));
+            asm volatile("st.shared.u32 [%0], %1;" :: "r"(base + LY::LIST + 4u * pos), "r"(tid) : "memory");
+        }
+        __syncthreads();                                           // list complete
+        if (tid < total) {                                          // whole warps drop out: total is uniform
+            unsigned item;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(item) : "r"(base + LY::LIST + 4u * tid) : "memory");
+            Jac<F> r, q;
+            cmul_load<F>(r, base + item * LY::STRIDE);
+            cmul_load<F>(q, base + item * LY::STRIDE + LY::PT);
+            jac_add(r, r, q);
+            cmul_store<F>(base + item * LY::STRIDE, r);
+        }
+        __syncthreads();                                           // additions stored before the next doubling; list / counts reusable
+    }
+    if (live) {
+        Jac<F> r;
+        cmul_load<F>(r, base + tid * LY::STRIDE);
+        out[i] = r;
+    }
+}
 // (p * k).normalize() by the signed 4-bit window (jac_mul_normalized, bn_curve.cuh); the 8-entry table lives in local memory
 template <class F>
 BN_KERNEL k_jac_mul_window(const Jac<F>* __restrict__ p, const Fq* __restrict__ fr, Jac<F>* __restrict__ out, size_t n) {

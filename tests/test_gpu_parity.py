@@ -199,6 +199,31 @@ def test_scalar_mul_vs_oracle(eng):
     assert eng.g1_normalize(inf).tobytes() == inf.tobytes()
 
 
+@pytest.mark.parametrize("n", [256, 257, 300, 1000])
+def test_scalar_mul_block_compacted_additions(eng, n):
+    """k_jac_mul_compact (a block's additions compacted onto full warps) replays the reference's exact double/add sequence per
+    scalar: raw Jacobian bytes equal the oracle's and the thread-per-scalar kernel's (mul_compact = 0), at sizes that leave the
+    last block ragged, with scalars 0, 1, 2, r-1, 2^k, all-ones runs, and bases at infinity / with z == 1."""
+    import paritytech_bn_b200 as bn
+    R = o.R_ORDER
+    ks = [0, 1, 2, R - 1, 1 << 200, (1 << 253) - 1, 0x5555555555555555555555555555555555555555555555555555555555555555 % R,
+          0xaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaaa % R, 3, 1 << 253] + util.scalars(n, stream=17)
+    fr = util.fr_bytes(ks[:n])
+    b1, b2 = _workload(64, 18)
+    idx = np.arange(n) % 64
+    g1 = b1.reshape(64, G1)[idx].copy(); g2 = b2.reshape(64, G2)[idx].copy()
+    g1[12], g2[12] = util.G1_INF, util.G2_INF
+    g1[13], g2[13] = util.G1_GEN, util.G2_GEN
+    g1, g2 = g1.reshape(-1), g2.reshape(-1)
+    e0, e2 = bn.Engine(0, mul_compact=0), bn.Engine(0, mul_compact=2)      # thread per scalar / compacted for G1 and G2
+    try:
+        got1, got2 = e2.g1_mul(g1, fr), e2.g2_mul(g2, fr)
+        assert got1.tobytes() == c.g1_mul(g1, fr).tobytes() == e0.g1_mul(g1, fr).tobytes() == eng.g1_mul(g1, fr).tobytes()
+        assert got2.tobytes() == c.g2_mul(g2, fr).tobytes() == e0.g2_mul(g2, fr).tobytes() == eng.g2_mul(g2, fr).tobytes()
+    finally:
+        e0.close(); e2.close()
+
+
 def test_scalar_mul_normalized_vs_oracle(eng):
     """bn254_g{1,2}_mul_normalized_many (signed-window kernel) == the oracle's (p * k).normalize(): edge scalars, extreme
     window digits, z == 1 bases and points at infinity next to random inputs."""
