@@ -631,18 +631,7 @@ def sharded_product(args, eng, util, torch, dist, dev, rank, world, host_barrier
     A, B = util.fr_images(half, stream=401), util.fr_images(half, stream=402)
     lo, hi = n * rank // world, n * (rank + 1) // world
 
-    def scal(i0, i1):
-        """(G1 scalar images, G2 scalar images) of the global pair indices [i0, i1)."""
-        s1, s2 = [], []
-        if i0 < half:
-            e = min(i1, half)
-            s1.append(A[i0 * FR:e * FR]); s2.append(B[i0 * FR:e * FR])
-        if i1 > half:
-            b = max(i0, half) - half
-            s1.append(util.neg_fr_images(B[b * FR:(i1 - half) * FR])); s2.append(A[b * FR:(i1 - half) * FR])
-        return np.concatenate(s1), np.concatenate(s2)
-
-    f1, f2 = scal(lo, hi)
+    f1, f2 = util.cancelling_pair_scalars(A, B, lo, hi)
     cnt = hi - lo
     d_g1, d_g2 = gen_points(f1, f2)
     d_part = torch.empty(GT, dtype=torch.uint8, device=dev)

@@ -55,6 +55,13 @@ struct bn254_ctx {
     bn254_ctx_options opt;   // resolved switches (no -1 left)
     std::recursive_mutex mu; // every entry point holds it: one context serialises its callers
 };
+// worker threads of the device-list entry points: joined on every exit path (a std::thread destroyed while joinable terminates
+// the process; creating the k-th thread can throw after k - 1 are running)
+struct Workers {
+    std::vector<std::thread> th;
+    ~Workers() { join(); }
+    void join() { for (auto& t : th) if (t.joinable()) t.join(); }
+};
 struct bn254_g2precomp {
     int device;
     size_t n;
@@ -610,7 +617,8 @@ int bn254_pairing_many_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1, c
     if (n_ctx == 1) { ENTER(ctxs[0]); return pairing_many_host(ctxs[0], g1, g2, gt_out, n); }
     struct Result { int rc = 0; char err[320] = ""; };
     std::vector<Result> res(n_ctx);
-    std::vector<std::thread> th;
+    Workers workers;
+    std::vector<std::thread>& th = workers.th;
     th.reserve(n_ctx);
     for (size_t d = 0; d < n_ctx; d++) {
         size_t lo = n * d / n_ctx, hi = n * (d + 1) / n_ctx;
@@ -629,7 +637,7 @@ int bn254_pairing_many_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1, c
             if (rc != 0) snprintf(res[d].err, sizeof res[d].err, "device %d: %s", c->device, g_err);   // g_err is this worker's
         });
     }
-    for (auto& t : th) t.join();
+    workers.join();
     for (size_t d = 0; d < n_ctx; d++) if (res[d].rc != 0) return fail(res[d].rc, res[d].err);
     return 0;
     API_END
@@ -1351,7 +1359,8 @@ static int product_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1, const
     struct Shard { int rc = 0; char err[320] = ""; Fq12* res = nullptr; };
     std::vector<Shard> sh(n_ctx);
     double t0 = now_ms();
-    std::vector<std::thread> th;
+    Workers workers;
+    std::vector<std::thread>& th = workers.th;
     th.reserve(n_ctx);
     for (size_t d = 0; d < n_ctx; d++) {
         size_t lo = n * d / n_ctx, cnt = n * (d + 1) / n_ctx - lo;
@@ -1379,7 +1388,7 @@ static int product_sharded(bn254_ctx** ctxs, size_t n_ctx, const void* g1, const
             if (rc != 0) snprintf(sh[d].err, sizeof sh[d].err, "device %d: %s", c->device, g_err);
         });
     }
-    for (auto& t : th) t.join();
+    workers.join();
     for (size_t d = 0; d < n_ctx; d++) if (sh[d].rc != 0) return fail(sh[d].rc, sh[d].err);
     double t1 = now_ms();
     // phase 2: gather on device 0 (peer copies over NVLink when the devices are peers; staged by the driver otherwise)

@@ -24,6 +24,36 @@ def test_shard_ranges_cover_and_are_contiguous():
             assert max(sizes) - min(sizes) <= 1
 
 
+def test_cancelling_pairs_construction_shards_for_any_world_size():
+    """bench.py's sharded_product (BASELINE configs[4]): the per-rank slices of the known-answer construction tile the whole
+    pair list for even AND odd world sizes (ranges crossing the half-way point), the scalars cancel (sum a_i b_i = 0 mod r),
+    and -- on a tiny instance through the oracle -- the product of all pairs is one while a rank's partial is not."""
+    import paritytech_bn_b200 as bn
+    from oracle import c_oracle as c
+    from tests import util
+    half = 9
+    A, B = util.fr_images(half, stream=401), util.fr_images(half, stream=402)
+    n = 2 * half
+    full1, full2 = util.cancelling_pair_scalars(A, B, 0, n)
+    rinv = pow(1 << 256, -1, util.R)
+
+    def canon(img):
+        return [int.from_bytes(img[i:i + 32].tobytes(), "little") * rinv % util.R for i in range(0, len(img), 32)]
+    a, b = canon(full1), canon(full2)
+    assert len(a) == n and sum(x * y for x, y in zip(a, b)) % util.R == 0
+    for world in (1, 2, 3, 4, 5, 7, 8):
+        parts = [util.cancelling_pair_scalars(A, B, *bn.shard_range(n, r, world)) for r in range(world)]
+        assert np.concatenate([p[0] for p in parts]).tobytes() == full1.tobytes()
+        assert np.concatenate([p[1] for p in parts]).tobytes() == full2.tobytes()
+    e1, e2 = util.cancelling_pair_scalars(A, B, 5, 5)
+    assert e1.size == 0 and e2.size == 0
+    g1 = c.g1_mul(np.tile(util.G1_GEN, n), full1)
+    g2 = c.g2_mul(np.tile(util.G2_GEN, n), full2)
+    assert c.pairing_batch(g1, g2).tobytes() == util.GT_ONE.tobytes()
+    lo, hi = bn.shard_range(n, 1, 3)
+    assert c.pairing_batch(g1[lo * 96:hi * 96], g2[lo * 192:hi * 192]).tobytes() != util.GT_ONE.tobytes()
+
+
 WORKER = textwrap.dedent('''
     import os, sys
     sys.path.insert(0, %(root)r)

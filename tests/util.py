@@ -68,6 +68,22 @@ def neg_fr_images(fr):
     return out.view(np.uint8).reshape(-1).copy()
 
 
+def cancelling_pair_scalars(A, B, i0, i1):
+    """Scalar images of the global pair indices [i0, i1) of the known-answer product of SURVEY 8e, n = 2 * len(A) pairs:
+    pair i < n/2 is (A_i G1, B_i G2), pair n/2 + j is ((-B_j) G1, A_j G2), so sum a_i b_i = 0 mod r and the whole product is
+    exactly one while any proper sub-range is not.  Returns (G1 scalar images, G2 scalar images) of the range."""
+    half = len(A) // 32
+    assert len(B) == len(A) and 0 <= i0 <= i1 <= 2 * half
+    s1, s2 = [np.zeros(0, dtype=np.uint8)], [np.zeros(0, dtype=np.uint8)]
+    if i0 < half:
+        e = min(i1, half)
+        s1.append(A[i0 * 32:e * 32]); s2.append(B[i0 * 32:e * 32])
+    if i1 > half:
+        b = max(i0, half) - half
+        s1.append(neg_fr_images(B[b * 32:(i1 - half) * 32])); s2.append(A[b * 32:(i1 - half) * 32])
+    return np.concatenate(s1), np.concatenate(s2)
+
+
 def fq_mont_bytes(vals):
     return b"".join((v * MONT % Q).to_bytes(32, "little") for v in vals)
 
