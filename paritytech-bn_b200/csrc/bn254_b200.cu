@@ -47,7 +47,9 @@ struct bn254_ctx {
     int sms = 148;     // multiprocessor count (the phase-synchronised kernels run one block per SM)
     cudaStream_t stream = nullptr;    // all work of the context; outranks stream2
     cudaStream_t stream2 = nullptr;   // second lane of the pipelined host-buffer pairing path
+    cudaStream_t stream34[2] = {nullptr, nullptr};   // lanes 3 and 4 (pipeline = 3 / 4)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
+    cudaEvent_t ev_join34[2] = {nullptr, nullptr};
     std::atomic<uint64_t> launches{0};
     Arena io;          // device copies of the host-pointer entry points' arguments and results
     Arena ws;          // kernel workspace: line-coefficient tables of the split Miller path, easy-part values
@@ -170,6 +172,7 @@ static int arena_reserve(bn254_ctx* ctx, Arena& a, size_t bytes, const char* wha
     if (a.p) {
         CU(cudaStreamSynchronize(ctx->stream));
         CU(cudaStreamSynchronize(ctx->stream2));
+        for (int k = 0; k < 2; k++) if (ctx->stream34[k]) CU(cudaStreamSynchronize(ctx->stream34[k]));
         cudaFree(a.p);
         a.p = nullptr; a.bytes = 0;
     }
@@ -218,7 +221,7 @@ const char* bn254_build_info(void) {
 void bn254_ctx_options_default(bn254_ctx_options* o) {
     if (!o) return;
     o->struct_size = (uint32_t)sizeof(bn254_ctx_options);
-    o->pipeline = env_int("BN254_PIPELINE", 1);
+    o->pipeline = env_int("BN254_PIPELINE", 4);
     o->big_blocks = env_int("BN254_BIG_BLOCKS", 1);
     o->fused_miller = env_int("BN254_FUSED_MILLER", 0);
     o->split_fexp = env_int("BN254_SPLIT_FEXP", 0);
@@ -237,6 +240,10 @@ void bn254_ctx_destroy(bn254_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
     if (ctx->stream2) { cudaStreamSynchronize(ctx->stream2); cudaStreamDestroy(ctx->stream2); }
+    for (int k = 0; k < 2; k++) {
+        if (ctx->stream34[k]) { cudaStreamSynchronize(ctx->stream34[k]); cudaStreamDestroy(ctx->stream34[k]); }
+        if (ctx->ev_join34[k]) cudaEventDestroy(ctx->ev_join34[k]);
+    }
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     if (ctx->ev_done) cudaEventDestroy(ctx->ev_done);
@@ -282,6 +289,10 @@ static int ctx_init(bn254_ctx* c, int device, const bn254_ctx_options* user) {
     cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
     CU(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_greatest));
     CU(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prio_least));
+    for (int k = 0; k < 2; k++) {
+        CU(cudaStreamCreateWithPriority(&c->stream34[k], cudaStreamNonBlocking, prio_least));
+        CU(cudaEventCreateWithFlags(&c->ev_join34[k], cudaEventDisableTiming));
+    }
     CU(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&c->ev_done, cudaEventDisableTiming));
@@ -572,27 +583,39 @@ static int pairing_many_host(bn254_ctx* ctx, const void* g1, const void* g2, voi
         CU(cudaStreamSynchronize(ctx->stream));
         return 0;
     }
-    // Two half batches on two lanes.  The one-wave kernels of the slot-file path finish all their blocks together, so a
-    // single batch exposes both transfers completely (inputs before the first kernel, results after the last one).  With two
-    // halves the second half's inputs travel while the first computes; each half's 448-thread kernels occupy half of the SMs.
-    // The first half is a whole number of blocks.
-    size_t nA = ((n / 2 + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK) * BN_FEXP_BLOCK, nB = n - nA;
-    size_t wA = miller_ws_bytes(nA), wB = miller_ws_bytes(nB);
-    if (fexp_ws_bytes(nA) > wA) wA = fexp_ws_bytes(nA);
-    if (fexp_ws_bytes(nB) > wB) wB = fexp_ws_bytes(nB);
-    wA = (wA + 255) & ~(size_t)255;
-    TRY(arena_reserve(ctx, ctx->ws, wA + wB, "cudaMalloc workspace"));
-    // one-wave batches: each half on its own SMs with full blocks (two smaller blocks per SM would interleave their phases);
+    // K part batches on K lanes (pipeline = 2, 3 or 4; default 4: +0.3 % at 2^16, +1.8 % at 2^18, +0.8 % at N = 8 over two).  The one-wave kernels of the slot-file path finish all their
+    // blocks together, so a single batch exposes both transfers completely (inputs before the first kernel, results after the
+    // last one).  With K parts the later parts' inputs travel while the first computes; each part's 448-thread kernels occupy
+    // 1/K of the SMs.  Every part but the last is a whole number of blocks.
+    int K = ctx->opt.pipeline < 2 ? 2 : ctx->opt.pipeline > 4 ? 4 : ctx->opt.pipeline;
+    size_t part = (((n + K - 1) / K + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK) * BN_FEXP_BLOCK;
+    size_t lo[4], cnt[4], woff[4], wsz[4], wtot = 0;
+    int parts = 0;
+    for (size_t at = 0; at < n && parts < K; parts++) {
+        size_t m = (parts == K - 1 || n - at < part) ? n - at : part;
+        lo[parts] = at; cnt[parts] = m; at += m;
+        size_t w = miller_ws_bytes(m);
+        if (fexp_ws_bytes(m) > w) w = fexp_ws_bytes(m);
+        w = (w + 255) & ~(size_t)255;
+        woff[parts] = wtot; wsz[parts] = w; wtot += w;
+    }
+    TRY(arena_reserve(ctx, ctx->ws, wtot, "cudaMalloc workspace"));
+    // one-wave batches: each part on its own SMs with full blocks (smaller blocks sharing an SM would interleave their phases);
     // larger batches fill every SM with one block at a time anyway and keep the block size rule of sync_block
     unsigned fb = n <= (size_t)ctx->sms * BN_FEXP_BLOCK ? BN_FEXP_BLOCK : 0;
-    A.ws = ctx->ws.p; A.ws_bytes = wA; A.force_block = fb;
-    Lane B{ctx, ctx->stream2, (char*)ctx->ws.p + wA, wB, fb};
+    cudaStream_t lanes[4] = {ctx->stream, ctx->stream2, ctx->stream34[0], ctx->stream34[1]};
+    cudaEvent_t joins[4] = {nullptr, ctx->ev_join, ctx->ev_join34[0], ctx->ev_join34[1]};
     CU(cudaEventRecord(ctx->ev_fork, ctx->stream));
-    CU(cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
-    int rc = pairing_many_enqueue(A, (const char*)g1, (const char*)g2, (char*)gt_out, mapped, d, 0, nA);
-    if (rc == 0) rc = pairing_many_enqueue(B, (const char*)g1, (const char*)g2, (char*)gt_out, mapped, d, nA, nB);
-    cudaEventRecord(ctx->ev_join, ctx->stream2);
-    cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0);
+    for (int k = 1; k < parts; k++) CU(cudaStreamWaitEvent(lanes[k], ctx->ev_fork, 0));
+    int rc = 0;
+    for (int k = 0; k < parts && rc == 0; k++) {
+        Lane Lk{ctx, lanes[k], (char*)ctx->ws.p + woff[k], wsz[k], fb};
+        rc = pairing_many_enqueue(Lk, (const char*)g1, (const char*)g2, (char*)gt_out, mapped, d, lo[k], cnt[k]);
+    }
+    for (int k = 1; k < parts; k++) {
+        cudaEventRecord(joins[k], lanes[k]);
+        cudaStreamWaitEvent(ctx->stream, joins[k], 0);
+    }
     cudaError_t es = cudaStreamSynchronize(ctx->stream);
     if (rc != 0) return rc;
     if (es != cudaSuccess) return fail(BN254_ERR_CUDA, "cudaStreamSynchronize", es);
