@@ -92,6 +92,8 @@ typedef struct bn254_ctx_options {
     int32_t mul_compact;   /* BN254_MUL_COMPACT   1: G1 * Fr (reference sequence) compacts a block's additions onto full warps
                               (k_jac_mul_compact, +6 %); 2: G2 * Fr as well (no gain, tests); 0: one thread per scalar with its
                               own `if (bit) add` (k_jac_mul).  Same Jacobian bytes in every mode. */
+    int32_t coop4_max_n;   /* BN254_COOP4_MAX_N   batches of at most this many units (default 592 = 4 per SM) take the quad-lane
+                              executor of the cooperative microcode: four warps per pairing, lowest latency; 0 disables */
 } bn254_ctx_options;
 void bn254_ctx_options_default(bn254_ctx_options* opt);
 int bn254_ctx_create(int device, bn254_ctx** out);

@@ -96,7 +96,7 @@ class CtxOptions(ctypes.Structure):
     """bn254_ctx_options (include/bn254_b200.h): -1 = library default."""
     _fields_ = [("struct_size", ctypes.c_uint32)] + [(k, ctypes.c_int32) for k in (
         "pipeline", "big_blocks", "fused_miller", "split_fexp", "fexp_smem", "miller_smem", "lines_smem", "subgroup_ref",
-        "zerocopy_out", "coop_max_n", "stack_bytes", "mul_compact")]
+        "zerocopy_out", "coop_max_n", "stack_bytes", "mul_compact", "coop4_max_n")]
 
     def __init__(self, **kw):
         super().__init__()

@@ -233,6 +233,7 @@ void bn254_ctx_options_default(bn254_ctx_options* o) {
     o->coop_max_n = env_int("BN254_COOP_MAX_N", BN_COOP_DEFAULT_MAX_N);
     o->stack_bytes = env_int("BN254_STACK_BYTES", 0);
     o->mul_compact = env_int("BN254_MUL_COMPACT", 1);
+    o->coop4_max_n = env_int("BN254_COOP4_MAX_N", BN_COOP4_DEFAULT_MAX_N);
 }
 
 void bn254_ctx_destroy(bn254_ctx* ctx) {
@@ -284,6 +285,8 @@ static int ctx_init(bn254_ctx* c, int device, const bn254_ctx_options* user) {
     CU(cudaFuncSetAttribute(k_jac_mul_compact<FqOps>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CmulLayout<FqOps>::BYTES));
     CU(cudaFuncSetAttribute(k_jac_mul_compact<Fq2Ops>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)CmulLayout<Fq2Ops>::BYTES));
     CU(cudaFuncSetAttribute(k_coop_gt_pow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BN_COOP_SMEM(BN_COOP_MAX_WARPS)));
+    CU(cudaFuncSetAttribute(k_coop4_pairing, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BN_COOP4_SMEM(BN_COOP4_MAX_GROUPS)));
+    CU(cudaFuncSetAttribute(k_coop4_gt_pow, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BN_COOP4_SMEM(BN_COOP4_MAX_GROUPS)));
     // the main stream outranks the second one: in the pipelined path the first half batch gets ahead of the second
     int prio_least = 0, prio_greatest = 0;
     cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
@@ -344,8 +347,22 @@ uint64_t bn254_ctx_launch_count(const bn254_ctx* ctx) { return ctx ? ctx->launch
 // thread per pairing.  Same bytes as the throughput path.
 static inline bool use_coop(const bn254_ctx* ctx, size_t n) { return ctx->opt.coop_max_n > 0 && n <= (size_t)ctx->opt.coop_max_n; }
 // mode 0: pairing, 1: Miller value (+ ok flags), 2: final exponentiation (g1 = the Gt input; ok = Option flags)
+// quad-lane executor (bn_coop4.cuh): four warps per unit, for batches of at most coop4_max_n units (a subset of the above)
+static inline bool use_coop4(const bn254_ctx* ctx, size_t n) { return use_coop(ctx, n) && n <= (size_t)(ctx->opt.coop4_max_n > 0 ? ctx->opt.coop4_max_n : 0); }
+// units per block and blocks of a quad-lane launch: the batch spread over all SMs, at most BN_COOP4_MAX_GROUPS per block
+static inline void coop4_shape(const bn254_ctx* ctx, size_t n, unsigned& groups, unsigned& grid) {
+    size_t per_sm = (n + (size_t)ctx->sms - 1) / (size_t)ctx->sms;
+    groups = per_sm < 1 ? 1u : per_sm > BN_COOP4_MAX_GROUPS ? (unsigned)BN_COOP4_MAX_GROUPS : (unsigned)per_sm;
+    grid = (unsigned)((n + groups - 1) / groups);
+}
 static int coop_pairing_dev(const Lane& L, const void* d_g1, const G2* d_g2, Fq12* d_out, uint8_t* d_ok, size_t n, int mode,
                             uint8_t* d_is_one = nullptr) {
+    if (use_coop4(L.ctx, n)) {
+        unsigned groups, g;
+        coop4_shape(L.ctx, n, groups, g);
+        LAUNCH_SYNC(L, k_coop4_pairing, g, groups * BN_COOP4_GROUP, BN_COOP4_SMEM(groups), d_g1, d_g2, d_out, d_ok, d_is_one, n, mode);
+        return 0;
+    }
     size_t per_sm = (n + (size_t)L.ctx->sms - 1) / (size_t)L.ctx->sms;
     unsigned warps = per_sm < 1 ? 1u : per_sm > BN_COOP_MAX_WARPS ? (unsigned)BN_COOP_MAX_WARPS : (unsigned)per_sm;
     unsigned g = (unsigned)((n + warps - 1) / warps);
@@ -960,6 +977,12 @@ int bn254_gt_pow_many(bn254_ctx* ctx, const void* a, const void* fr, void* out, 
     ENTER(ctx);
     if (n && (!a || !fr || !out)) return fail(BN254_ERR_ARG, "null pointer");
     return gt_host(ctx, a, fr, sizeof(Fq), out, nullptr, n, [&](const Lane& L, void** d) -> int {
+        if (use_coop4(ctx, n)) {  // smallest batches: four warps per element (k_coop4_gt_pow)
+            unsigned groups, g;
+            coop4_shape(ctx, n, groups, g);
+            LAUNCH_SYNC(L, k_coop4_gt_pow, g, groups * BN_COOP4_GROUP, BN_COOP4_SMEM(groups), (const Fq12*)d[0], (const Fq*)d[1], (Fq12*)d[2], n);
+            return 0;
+        }
         if (use_coop(ctx, n)) {   // small batches: one warp per element (k_coop_gt_pow)
             size_t per_sm = (n + (size_t)ctx->sms - 1) / (size_t)ctx->sms;
             unsigned warps = per_sm > BN_COOP_MAX_WARPS ? (unsigned)BN_COOP_MAX_WARPS : (unsigned)per_sm;

@@ -6,7 +6,7 @@
 #include "bn_wire.cuh"
 #include "bn_slots.cuh"
 #include "bn_slots_curve.cuh"
-#include "bn_coop.cuh"
+#include "bn_coop4.cuh"
 
 namespace bn {
 

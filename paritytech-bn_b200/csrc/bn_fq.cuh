@@ -233,6 +233,95 @@ template <bool MINUS> BN_HD void fq_lin9(Fq& r, const Fq& a, const Fq& b) {
     for (int i = 0; i < 8; i++) r.v[i] = o[i];
 #endif
 }
+// ---- sums without a reduction per term (the quad-lane executor, bn_coop4.cuh) --------------------------------------
+// A 288-bit two's-complement accumulator: up to 8 signed terms in [0, q) and one multiplication by 9 stay far inside it.
+// acc9_add: a += x (mask = 0) or a -= x (mask = 0xffffffff) as ~x + 1.  acc9_reduce: (a + offset_q * q) mod q for a total in
+// [0, 160 q) (fq_red9_ptx: quotient estimate from the top bits + one conditional subtraction, tools/gen_fq_ptx.py).
+struct Acc9 { uint32_t v[9]; };
+BN_HD void acc9_zero(Acc9& a) {
+#pragma unroll
+    for (int i = 0; i < 9; i++) a.v[i] = 0;
+}
+BN_HD void acc9_add(Acc9& a, const Fq& x, uint32_t mask) {
+#if defined(__CUDA_ARCH__)
+    asm("{\n\t.reg .u32 d;\n\t"
+        "add.cc.u32 d, %17, 1;\n\t"                  // carry in = 1 when subtracting
+        "addc.cc.u32 %0, %0, %9;\n\taddc.cc.u32 %1, %1, %10;\n\taddc.cc.u32 %2, %2, %11;\n\taddc.cc.u32 %3, %3, %12;\n\t"
+        "addc.cc.u32 %4, %4, %13;\n\taddc.cc.u32 %5, %5, %14;\n\taddc.cc.u32 %6, %6, %15;\n\taddc.cc.u32 %7, %7, %16;\n\t"
+        "addc.u32 %8, %8, %17;\n\t}"
+        : "+r"(a.v[0]), "+r"(a.v[1]), "+r"(a.v[2]), "+r"(a.v[3]), "+r"(a.v[4]), "+r"(a.v[5]), "+r"(a.v[6]), "+r"(a.v[7]), "+r"(a.v[8])
+        : "r"(x.v[0] ^ mask), "r"(x.v[1] ^ mask), "r"(x.v[2] ^ mask), "r"(x.v[3] ^ mask), "r"(x.v[4] ^ mask), "r"(x.v[5] ^ mask),
+          "r"(x.v[6] ^ mask), "r"(x.v[7] ^ mask), "r"(mask));
+#else
+    uint64_t c = mask & 1u;
+    for (int i = 0; i < 9; i++) {
+        uint64_t s = (uint64_t)a.v[i] + (i < 8 ? (x.v[i] ^ mask) : mask) + c;
+        a.v[i] = (uint32_t)s;
+        c = s >> 32;
+    }
+#endif
+}
+// a += b (mod 2^288)
+BN_HD void acc9_addv(Acc9& a, const Acc9& b) {
+#if defined(__CUDA_ARCH__)
+    asm("add.cc.u32 %0, %0, %9;\n\taddc.cc.u32 %1, %1, %10;\n\taddc.cc.u32 %2, %2, %11;\n\taddc.cc.u32 %3, %3, %12;\n\t"
+        "addc.cc.u32 %4, %4, %13;\n\taddc.cc.u32 %5, %5, %14;\n\taddc.cc.u32 %6, %6, %15;\n\taddc.cc.u32 %7, %7, %16;\n\t"
+        "addc.u32 %8, %8, %17;"
+        : "+r"(a.v[0]), "+r"(a.v[1]), "+r"(a.v[2]), "+r"(a.v[3]), "+r"(a.v[4]), "+r"(a.v[5]), "+r"(a.v[6]), "+r"(a.v[7]), "+r"(a.v[8])
+        : "r"(b.v[0]), "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]), "r"(b.v[8]));
+#else
+    uint64_t c = 0;
+    for (int i = 0; i < 9; i++) {
+        uint64_t s = (uint64_t)a.v[i] + b.v[i] + c;
+        a.v[i] = (uint32_t)s;
+        c = s >> 32;
+    }
+#endif
+}
+// a += 9 b (mod 2^288): b + (b << 3)
+BN_HD void acc9_add9(Acc9& a, const Acc9& b) {
+    Acc9 s;
+    s.v[0] = b.v[0] << 3;
+#pragma unroll
+    for (int i = 1; i < 9; i++) s.v[i] = (b.v[i] << 3) | (b.v[i - 1] >> 29);
+    acc9_addv(a, b);
+    acc9_addv(a, s);
+}
+// limb i of m q for m = 8 and m = 80 (the offsets that make the sums of the MUL and LIN steps non-negative)
+BN_HD uint32_t acc9_offset_limb(int m80, int i) {
+    // 8 q and 80 q over nine limbs
+    const uint32_t q8[9] = {0xc3e7ea38u, 0xe10460b6u, 0x438e5469u, 0xbc0b548bu, 0x0c0ac2ecu, 0xc2822db4u, 0x098d014du, 0x83227397u, 0x00000001u};
+    const uint32_t q80[9] = {0xa70f2630u, 0xca2bc723u, 0xa38f4c22u, 0x58714d70u, 0x786b9d3fu, 0x9915c908u, 0x5f820d09u, 0x1f5883e6u, 0x0000000fu};
+    return m80 ? q80[i] : q8[i];
+}
+template <bool M80> BN_HD void acc9_reduce(Fq& r, const Acc9& a) {
+    Acc9 t = a, off;
+#pragma unroll
+    for (int i = 0; i < 9; i++) off.v[i] = acc9_offset_limb(M80 ? 1 : 0, i);
+    acc9_addv(t, off);
+#if defined(__CUDA_ARCH__)
+    uint32_t o[8];
+    fq_red9_ptx(o, t.v);
+#pragma unroll
+    for (int i = 0; i < 8; i++) r.v[i] = o[i];
+#else
+    uint32_t th = (t.v[8] << 14) | (t.v[7] >> 18);
+    uint32_t k = (uint32_t)(((uint64_t)th * 1386367u) >> 32);
+    int64_t br = 0;
+    uint64_t mc = 0;
+    uint32_t o[8];
+    for (int i = 0; i < 8; i++) {
+        uint64_t m = (uint64_t)fq_modulus_limb(i) * k + mc;
+        mc = m >> 32;
+        int64_t d = (int64_t)t.v[i] - (int64_t)(uint32_t)m + br;
+        o[i] = (uint32_t)d;
+        br = d >> 32;
+    }
+    if (hostimpl::geq_q(o)) hostimpl::sub_q(o);
+    for (int i = 0; i < 8; i++) r.v[i] = o[i];
+#endif
+}
+
 BN_HD void fq_neg(Fq& r, const Fq& a) {  // src/arith.rs:309-316 (0 -> 0)
     Fq z;
     fq_set_zero(z);

@@ -14,7 +14,8 @@ from tests import util  # noqa: E402
 
 sizes = [int(x) for x in sys.argv[1:]] or [8, 449, 1600]
 eng = bn.Engine(0, coop_max_n=0)          # the slot-file kernels (one thread per pairing) at small sizes
-coop = bn.Engine(0)                       # default: batches this small run one warp per pairing (k_coop_pairing)
+coop = bn.Engine(0, coop4_max_n=0)        # one warp per pairing (k_coop_pairing)
+quad = bn.Engine(0)                       # default: batches of at most 592 run four warps per pairing (k_coop4_pairing), larger ones one warp
 for n in sizes:
     g1, g2 = util.points_cpu(util.scalars(n, stream=71), util.scalars(n, stream=72))
     g1 = g1.reshape(n, 96).copy()
@@ -22,11 +23,21 @@ for n in sizes:
     g1 = g1.reshape(-1)
     m = min(n, 64)
     exp = c.pairing_many(g1[:m * 96], g2[:m * 192]).tobytes()
-    for name, e in (("slot-file", eng), ("warp-cooperative", coop)):
+    for name, e in (("slot-file", eng), ("warp-cooperative", coop), ("quad-lane / default", quad)):
         got = e.pairing(g1, g2)
         assert got[:m * 384].tobytes() == exp, (name, n)
         print("pairing n=%d %s ok" % (n, name), flush=True)
+    if n <= 8:
+        ks = util.fr_bytes(util.scalars(n, stream=76))
+        want = c.gt_pow(got, ks).tobytes()
+        for name, e in (("warp-cooperative", coop), ("quad-lane", quad)):
+            assert e.gt_pow(got, ks).tobytes() == want, (name, n)
+            ml, _ = e.miller_loop_many(g2, g1)
+            fe, _ = e.final_exponentiation(ml)
+            assert fe.tobytes() == got.tobytes(), (name, n)
+        print("gt_pow / miller / final exp n=%d on both cooperative executors ok" % n, flush=True)
 coop.close()
+quad.close()
 w = util.groth16_checks(70)
 out, is_one = eng.pairing_batch(w["g1"], w["g2"], pairs_per_check=4)
 rout, ris = c.pairing_product_many(w["g1"], w["g2"], 4)

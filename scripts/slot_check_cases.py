@@ -23,7 +23,7 @@ eng = bn.Engine(0)
 print("library:", bn.library_path(), flush=True)
 eng._check(eng.lib.bn254_debug_slot_reset(eng.ctx))
 assert counter(eng)[0] == 0
-# the cases: pairings on the slot-file kernels and on the warp-cooperative kernel at n = 8, 449, 1600; product checks flat and
+# the cases: pairings on the slot-file kernels, the warp-cooperative and the quad-lane kernels at n = 8, 449, 1600 (+ Gt::pow at 8); product checks flat and
 # with shared tables; 512-thread blocks on 6 slots; window scalar multiplication; sharded product / pairing over two contexts
 # (run in THIS process: the counter is a device global of the library image loaded here)
 import runpy  # noqa: E402

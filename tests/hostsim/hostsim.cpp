@@ -29,6 +29,17 @@ UN(fq12_final_exp_last_chunk, Fq12, fq12_final_exp_last_chunk)
 BIN(g1_add, G1, jac_add) BIN(g2_add, G2, jac_add) UN(g1_double, G1, jac_double) UN(g2_double, G2, jac_double)
 UN(g1_normalize, G1, jac_normalize) UN(g2_normalize, G2, jac_normalize)
 
+// lazy sums of the quad-lane executor: out = sum_k +-terms[k] (signs bit k) [+ 9 * sum_k +-xterms[k]] mod q
+extern "C" void hs_acc9_sum(const void* terms, unsigned nterms, unsigned signs, const void* xterms, unsigned nx, unsigned xsigns, void* o) {
+    Acc9 a, x;
+    acc9_zero(a); acc9_zero(x);
+    for (unsigned k = 0; k < nterms; k++) acc9_add(a, ld<Fq>(terms, k), (signs >> k) & 1u ? 0xffffffffu : 0u);
+    for (unsigned k = 0; k < nx; k++) acc9_add(x, ld<Fq>(xterms, k), (xsigns >> k) & 1u ? 0xffffffffu : 0u);
+    Fq r;
+    if (nx) { acc9_add9(a, x); acc9_reduce<true>(r, a); } else acc9_reduce<false>(r, a);
+    st(o, 0, r);
+}
+
 UN(g1_neg, G1, jac_neg) UN(g2_neg, G2, jac_neg)
 extern "C" void hs_g1_eq(const void* a, const void* b, unsigned char* eq, size_t n) {
     for (size_t i = 0; i < n; i++) { G1 x = ld<G1>(a, i), y = ld<G1>(b, i); eq[i] = jac_eq(x, y); }

@@ -456,11 +456,21 @@ def test_abi_smoke_compiled_c_consumer():
     assert "abi_smoke ok" in p.stdout
 
 
-@pytest.mark.parametrize("n", [1, 3, 17, 149, 2368])
-def test_warp_cooperative_latency_path(eng, n):
-    """Batches of at most coop_max_n pairings run one WARP per pairing (k_coop_pairing executing the generated microcode):
-    pairing, miller_loop_many, final_exponentiation (incl. zero -> None) and small pairing_batch products give the oracle's
-    bytes, the same bytes as the one-thread-per-pairing kernels (coop_max_n = 0), with points at infinity and z == 1."""
+@pytest.mark.parametrize("n,quad", [(1, 1), (3, 1), (17, 1), (149, 1), (592, 1), (1, 0), (3, 0), (17, 0), (149, 0), (2368, 0)])
+def test_warp_cooperative_latency_path(n, quad):
+    """Batches of at most coop_max_n pairings run the generated microcode: four warps per pairing up to coop4_max_n = 592
+    (k_coop4_pairing, quad = 1: one to four pairings per block), one warp per pairing above (k_coop_pairing, quad = 0 forces it):
+    pairing, miller_loop_many, final_exponentiation (incl. zero -> None), Gt::pow and small pairing_batch products give the
+    oracle's bytes, the same bytes as the one-thread-per-pairing kernels (coop_max_n = 0), with points at infinity and z == 1."""
+    import paritytech_bn_b200 as bn
+    eng = bn.Engine(0) if quad else bn.Engine(0, coop4_max_n=0)
+    try:
+        _cooperative_case(eng, n)
+    finally:
+        eng.close()
+
+
+def _cooperative_case(eng, n):
     import paritytech_bn_b200 as bn
     base = min(n, 256)
     p1, p2 = util.points_cpu(util.scalars(base, stream=91), util.scalars(base, stream=92))

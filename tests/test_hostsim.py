@@ -335,3 +335,33 @@ def test_wire_from_compressed_host_build():
             assert st.tobytes() == so.tobytes()
             assert out.tobytes() == ro.tobytes()
             assert set(st) >= {0, 1, 2, 3}
+
+
+def test_lazy_sums_of_the_quad_lane_executor():
+    """acc9_add / acc9_add9 / acc9_reduce (csrc/bn_fq.cuh; the device side ends in fq_red9_ptx, swept by tools/gen_fq_ptx.py): up to
+    8 signed terms, optionally plus 9 times a second signed sum, reduced once -- against Python integers, extremes included."""
+    lib = hostsim.lib()
+
+    def le(v):
+        return np.frombuffer(int(v).to_bytes(32, "little"), dtype=np.uint8)
+
+    def run(ts, signs, xs, xsigns):
+        t = np.concatenate([le(v) for v in ts] + [np.zeros(0, np.uint8)]) if ts else np.zeros(32, np.uint8)
+        x = np.concatenate([le(v) for v in xs]) if xs else np.zeros(32, np.uint8)
+        out = np.zeros(32, np.uint8)
+        lib.hs_acc9_sum(_p(t), len(ts), signs, _p(x), len(xs), xsigns, _p(out))
+        exp = sum(-v if (signs >> k) & 1 else v for k, v in enumerate(ts)) + 9 * sum(-v if (xsigns >> k) & 1 else v for k, v in enumerate(xs))
+        assert int.from_bytes(out.tobytes(), "little") == exp % o.Q, (ts, signs, xs, xsigns)
+
+    big = o.Q - 1
+    for n in range(0, 9):
+        run([big] * n, 0, [], 0)                    # 8 (q - 1), the largest plain sum
+        run([big] * n, (1 << n) - 1, [], 0)         # -8 (q - 1), the smallest
+        for nx in range(1, 9 - n):
+            run([big] * n, 0, [big] * nx, 0)
+            run([big] * n, (1 << n) - 1, [big] * nx, (1 << nx) - 1)
+            run([0] * n, 0, [0] * nx, 0)
+    for _ in range(3000):
+        n = rng.randrange(0, 9)
+        nx = rng.randrange(0, 9 - n)
+        run([rfq() for _ in range(n)], rng.randrange(1 << n) if n else 0, [rfq() for _ in range(nx)], rng.randrange(1 << nx) if nx else 0)

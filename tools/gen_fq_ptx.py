@@ -434,6 +434,34 @@ def gen_lin9(minus):
     return P
 
 
+def gen_red9():
+    """r = t mod q for a 9-limb t < 160 q: the reduction tail of gen_lin9 on its own, for sums accumulated WITHOUT a conditional
+    subtraction per term (the quad-lane executor, csrc/bn_coop4.cuh: up to 8 signed terms and one multiplication by xi = 9 + u,
+    offset by a multiple of q so that the total is non-negative).  Same quotient estimate from the top bits,
+    k = ((t >> 242) * floor(2^32 / 3098)) >> 32 with k <= floor(t / q) <= k + 1 (swept below over every top word up to 160 q)."""
+    P = Prog("fq_red9_ptx")
+    t = ["a%d" % i for i in range(9)]
+    r = ["r%d" % i for i in range(8)]
+    P.inputs = t
+    P.outputs = r
+    x, th, k = P.tmp(), P.tmp(), P.tmp()
+    P.emit("shr", x, t[7], 18)
+    P.emit("mad.lo", th, t[8], 1 << 14, x)
+    P.emit("mul.hi", k, th, KMUL)
+    for j in range(4):
+        P.emit("mad.lo.cc" if j == 0 else "madc.lo.cc", r[2 * j], NQL[2 * j], k, t[2 * j])
+        P.emit("madc.hi.cc", r[2 * j + 1], NQL[2 * j], k, t[2 * j + 1])
+    for j in range(4):
+        P.emit("mad.lo.cc" if j == 0 else "madc.lo.cc", r[2 * j + 1], NQL[2 * j + 1], k, r[2 * j + 1])
+        if j < 3:
+            P.emit("madc.hi.cc", r[2 * j + 2], NQL[2 * j + 1], k, r[2 * j + 2])
+    cond_sub_q(P, r)
+    return P
+
+
+RED9_MAX = 160         # fq_red9_ptx accepts t < RED9_MAX * q
+
+
 def gen_wide_add():
     P = Prog("wide_add_ptx")
     a = ["a%d" % i for i in range(16)]
@@ -553,8 +581,27 @@ def check():
         if lo_t > hi_t:
             continue
         assert k <= lo_t // Q and hi_t // Q <= k + 1 and hi_t - k * Q < 2 * Q, th
-    print("simulated OK: %d mul/mulwide/add/sub pairs, 2000 redc/wide cases, %d 9a+-b cases" % (n, nl))
-    for p in (pm, pw, pr, pa, ps, pp, pn):
+    p9 = gen_red9()
+    n9 = 0
+    cases = []
+    for kq in range(0, RED9_MAX + 1):
+        for d in (-2, -1, 0, 1, 2, (1 << 224) - 1, -(1 << 224), 1 << 242, -(1 << 242)):
+            cases.append(kq * Q + d)
+    cases += [rng.randrange(RED9_MAX * Q) for _ in range(3000)]
+    for tv in cases:
+        if not 0 <= tv < RED9_MAX * Q:
+            continue
+        env = {("a%d" % i): v for i, v in enumerate(limbs(tv, 9))}
+        assert unl(p9.run(env), p9.outputs) == tv % Q, ("red9", hex(tv))
+        n9 += 1
+    for th in range(0, (RED9_MAX * Q >> 242) + 2):
+        k = (th * KMUL) >> 32
+        lo_t, hi_t = th << 242, min(((th + 1) << 242) - 1, RED9_MAX * Q - 1)
+        if lo_t > hi_t:
+            continue
+        assert k <= lo_t // Q and hi_t // Q <= k + 1 and hi_t - k * Q < 2 * Q, th
+    print("simulated OK: %d mul/mulwide/add/sub pairs, 2000 redc/wide cases, %d 9a+-b cases, %d 9-limb reductions" % (n, nl, n9))
+    for p in (pm, pw, pr, pa, ps, pp, pn, p9):
         ops = [op.split(".")[0] for op, _, _, _ in p.ins]
         print("  %-16s %3d PTX instrs (%d mad/mul)" % (p.name, len(p.ins), sum(o in ("mad", "madc", "mul") for o in ops)))
 
@@ -567,6 +614,10 @@ def emit_function(P, inout=False):
         sig = "uint32_t (&a)[%d], const uint32_t (&b)[%d]" % (nout, nin)
         outs = ", ".join('"+r"(a[%d])' % i for i in range(nout))
         ins = ", ".join('"r"(b[%d])' % i for i in range(nin))
+    elif P.name == "fq_red9_ptx":
+        sig = "uint32_t (&r)[8], const uint32_t (&t)[9]"
+        outs = ", ".join('"=&r"(r[%d])' % i for i in range(8))
+        ins = ", ".join('"r"(t[%d])' % i for i in range(9))
     elif P.name == "fq_redc_ptx":
         sig = "uint32_t (&r)[8], const uint32_t (&t)[16]"
         outs = ", ".join('"=&r"(r[%d])' % i for i in range(8))
@@ -592,7 +643,7 @@ def main():
                 "// generation time.  8x32-bit-limb BN254 Fq arithmetic as single inline-PTX carry-chain blocks.\n"
                 "// Outputs are early-clobber ('=&r'): they never alias an input register.\n"
                 "#pragma once\n#include <stdint.h>\n\n")
-        for P, io in ((gen_mul(), False), (gen_mulwide(), False), (gen_redc(), False), (gen_add(), False), (gen_sub(), False), (gen_lin9(False), False), (gen_lin9(True), False),
+        for P, io in ((gen_mul(), False), (gen_mulwide(), False), (gen_redc(), False), (gen_add(), False), (gen_sub(), False), (gen_lin9(False), False), (gen_lin9(True), False), (gen_red9(), False),
                       (gen_wide_add(), True), (gen_wide_sub(), True)):
             f.write(emit_function(P, io))
             f.write("\n")
