@@ -24,8 +24,8 @@ namespace bn {
 #define BN_HAVE_COOP 1
 #define BN_COOP_MAX_WARPS 16                                   /* 16 x 11,136 B of slots + 46 KB of tables = 224 KB: one block per SM */
 #define BN_COOP_SLOT_BYTES (BN_COOP_NSLOTS * 64)
-#define BN_COOP_CODE_WORDS (BN_COOP_NSTEPS * 160)
-#define BN_COOP_TABLE_WORDS ((BN_COOP_CODE_WORDS + BN_COOP_NSTEPS + BN_COOP_NTRACE + 3) & ~3)
+#define BN_COOP_CODE_WORDS (BN_COOP_NSTEPS_SEQ * 160)            /* the steps of this executor: a prefix of the table (the rest is bn_coop4.cuh's) */
+#define BN_COOP_TABLE_WORDS ((BN_COOP_CODE_WORDS + BN_COOP_NSTEPS_SEQ + BN_COOP_NTRACE + 3) & ~3)
 #define BN_COOP_SMEM(warps) ((size_t)BN_COOP_TABLE_WORDS * 4 + (size_t)(warps) * BN_COOP_SLOT_BYTES)
 #define BN_COOP_DEFAULT_MAX_N 2368                             /* up to one warp per pairing on every SM (148 x 16) */
 
@@ -137,8 +137,8 @@ __device__ __forceinline__ void coop_step(uint32_t tr, sp s_code, sp s_hdr, sp w
 __device__ __forceinline__ sp coop_load_tables() {
     uint32_t* dst = reinterpret_cast<uint32_t*>(bn_slot_mem);
     for (unsigned k = threadIdx.x; k < BN_COOP_CODE_WORDS; k += blockDim.x) dst[k] = bn_coop_code[k];
-    for (unsigned k = threadIdx.x; k < BN_COOP_NSTEPS; k += blockDim.x) dst[BN_COOP_CODE_WORDS + k] = bn_coop_hdr[k];
-    for (unsigned k = threadIdx.x; k < BN_COOP_NTRACE; k += blockDim.x) dst[BN_COOP_CODE_WORDS + BN_COOP_NSTEPS + k] = bn_coop_trace[k];
+    for (unsigned k = threadIdx.x; k < BN_COOP_NSTEPS_SEQ; k += blockDim.x) dst[BN_COOP_CODE_WORDS + k] = bn_coop_hdr[k];
+    for (unsigned k = threadIdx.x; k < BN_COOP_NTRACE; k += blockDim.x) dst[BN_COOP_CODE_WORDS + BN_COOP_NSTEPS_SEQ + k] = bn_coop_trace[k];
     __syncthreads();
     return (sp)__cvta_generic_to_shared(bn_slot_mem);
 }
@@ -158,7 +158,7 @@ __device__ __forceinline__ void coop_call(unsigned begin, unsigned count, uint32
 __global__ void __launch_bounds__(BN_COOP_MAX_WARPS * 32, 1) k_coop_pairing(const void* g1_or_gt, const G2* __restrict__ g2, Fq12* out,
                                                                             uint8_t* __restrict__ ok, uint8_t* __restrict__ is_one, size_t n, int mode) {
     const sp tab = coop_load_tables();
-    const sp s_code = tab, s_hdr = tab + 4u * BN_COOP_CODE_WORDS, s_trace = s_hdr + 4u * BN_COOP_NSTEPS;
+    const sp s_code = tab, s_hdr = tab + 4u * BN_COOP_CODE_WORDS, s_trace = s_hdr + 4u * BN_COOP_NSTEPS_SEQ;
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const size_t i = (size_t)blockIdx.x * (blockDim.x >> 5) + warp;
     if (i >= n) return;                                          // whole warps leave: nothing below synchronises the block

@@ -19,15 +19,17 @@
 namespace bn {
 
 #define BN_COOP4_GROUP 128u
-#define BN_COOP4_MAX_GROUPS 4                                  /* groups (pairings) per block: 46 KB of tables + 4 x 11,136 B */
-#define BN_COOP4_SMEM(groups) BN_COOP_SMEM(groups)
+#define BN_COOP4_MAX_GROUPS 4                                  /* groups (pairings) per block: 57 KB of tables + 4 x 11,136 B */
+#define BN_COOP4_CODE_WORDS (BN_COOP_NSTEPS * 160)                /* every step: the sequential routines and the paired ones */
+#define BN_COOP4_TABLE_WORDS ((BN_COOP4_CODE_WORDS + BN_COOP_NSTEPS + 2 * BN_COOP4_NTRACE + 3) & ~3)
+#define BN_COOP4_SMEM(groups) ((size_t)BN_COOP4_TABLE_WORDS * 4 + (size_t)(groups) * BN_COOP_SLOT_BYTES)
 #define BN_COOP4_DEFAULT_MAX_N 592                             /* 148 SMs x 4 groups */
 
 #ifdef BN_SLOT_CHECK
 __device__ __forceinline__ bool coop4_ok(sp a, unsigned bytes, bool write) {
     const sp dyn0 = (sp)__cvta_generic_to_shared(bn_slot_mem);
-    const sp file = dyn0 + 4u * BN_COOP_TABLE_WORDS + (threadIdx.x / BN_COOP4_GROUP) * BN_COOP_SLOT_BYTES;
-    if (!write && a < dyn0 + 4u * BN_COOP_TABLE_WORDS) return slot_ok(6u, a, bytes, dyn0, 4u * BN_COOP_TABLE_WORDS);
+    const sp file = dyn0 + 4u * BN_COOP4_TABLE_WORDS + (threadIdx.x / BN_COOP4_GROUP) * BN_COOP_SLOT_BYTES;
+    if (!write && a < dyn0 + 4u * BN_COOP4_TABLE_WORDS) return slot_ok(6u, a, bytes, dyn0, 4u * BN_COOP4_TABLE_WORDS);
     return slot_ok(write ? 8u : 7u, a, bytes, file, BN_COOP_SLOT_BYTES);
 }
 #endif
@@ -173,16 +175,26 @@ __device__ __forceinline__ void coop4_call(unsigned begin, unsigned count, uint3
     }
 }
 
+// the whole step table, its headers and the paired trace travel to shared memory once per block (57 KB)
+__device__ __forceinline__ sp coop4_load_tables() {
+    uint32_t* dst = reinterpret_cast<uint32_t*>(bn_slot_mem);
+    for (unsigned k = threadIdx.x; k < BN_COOP4_CODE_WORDS; k += blockDim.x) dst[k] = bn_coop_code[k];
+    for (unsigned k = threadIdx.x; k < BN_COOP_NSTEPS; k += blockDim.x) dst[BN_COOP4_CODE_WORDS + k] = bn_coop_hdr[k];
+    for (unsigned k = threadIdx.x; k < 2u * BN_COOP4_NTRACE; k += blockDim.x) dst[BN_COOP4_CODE_WORDS + BN_COOP_NSTEPS + k] = bn_coop4_trace[k];
+    __syncthreads();
+    return (sp)__cvta_generic_to_shared(bn_slot_mem);
+}
+
 // Modes, arguments and results of k_coop_pairing (bn_coop.cuh); `groups` pairings per block, 128 threads each.
 __global__ void __launch_bounds__(BN_COOP4_MAX_GROUPS * BN_COOP4_GROUP, 1) k_coop4_pairing(const void* g1_or_gt, const G2* __restrict__ g2,
                                   Fq12* out, uint8_t* __restrict__ ok, uint8_t* __restrict__ is_one, size_t n, int mode) {
-    const sp tab = coop_load_tables();
-    const sp s_code = tab, s_hdr = tab + 4u * BN_COOP_CODE_WORDS, s_trace = s_hdr + 4u * BN_COOP_NSTEPS;
+    const sp tab = coop4_load_tables();
+    const sp s_code = tab, s_hdr = tab + 4u * BN_COOP4_CODE_WORDS, s_trace = s_hdr + 4u * BN_COOP_NSTEPS;
     const unsigned group = threadIdx.x / BN_COOP4_GROUP, gt = threadIdx.x % BN_COOP4_GROUP;
     const unsigned vlane = ((((gt >> 5) + group) & 3u) << 3) | ((gt >> 2) & 7u), part = gt & 3u;   // lanes 0..7 (the busiest) of the block's groups on different sub-partitions
     const size_t i = (size_t)blockIdx.x * (blockDim.x / BN_COOP4_GROUP) + group;
     if (i >= n) return;                                          // whole groups leave: the barriers below are per group
-    const sp wbase = tab + 4u * BN_COOP_TABLE_WORDS + group * BN_COOP_SLOT_BYTES;
+    const sp wbase = tab + 4u * BN_COOP4_TABLE_WORDS + group * BN_COOP_SLOT_BYTES;
 
     for (unsigned k = gt; k < BN_COOP_NCONST * 16u; k += BN_COOP4_GROUP) q_sts32(wbase + 4u * k, bn_coop_const[k]);
     bool good = true;
@@ -193,7 +205,7 @@ __global__ void __launch_bounds__(BN_COOP4_MAX_GROUPS * BN_COOP4_GROUP, 1) k_coo
         for (unsigned k = 0; k < 96u; k++) any |= src[k];        // every thread the same words: a uniform decision
         for (unsigned k = gt; k < 96u; k += BN_COOP4_GROUP) q_sts32(wbase + 64u * BN_COOP_SLOT_F + 4u * k, src[k]);
         good = any != 0;                                         // zero has no final exponentiation (Option::None)
-        t_lo = BN_COOP_T_FEXP_BEGIN; t_hi = BN_COOP_T_FEXP_END;
+        t_lo = BN_COOP4_T_FEXP_BEGIN; t_hi = BN_COOP4_T_FEXP_END;
     } else {
         const uint32_t* p = reinterpret_cast<const uint32_t*>(reinterpret_cast<const G1*>(g1_or_gt) + i);
         const uint32_t* q = reinterpret_cast<const uint32_t*>(g2 + i);
@@ -206,15 +218,20 @@ __global__ void __launch_bounds__(BN_COOP4_MAX_GROUPS * BN_COOP4_GROUP, 1) k_coo
         for (unsigned w = 0; w < 8u; w++) pz |= p[16u + w];
         for (unsigned w = 0; w < 16u; w++) qz |= q[32u + w];
         good = pz != 0 && qz != 0;
-        t_lo = BN_COOP_T_PAIRING_BEGIN;
-        t_hi = mode == 1 ? BN_COOP_T_MILLER_END : BN_COOP_T_PAIRING_END;
+        t_lo = BN_COOP4_T_PAIRING_BEGIN;
+        t_hi = mode == 1 ? BN_COOP4_T_MILLER_END : BN_COOP4_T_PAIRING_END;
     }
     coop4_sync(group);
 
     if (good) {
 #pragma unroll 1
         for (int t = t_lo; t < t_hi; t++) {
-            coop4_step(q_lds32(s_trace + 4u * (unsigned)t), s_code, s_hdr, wbase, vlane, part);
+            // a paired entry: lanes 24..31 (one warp of the group) run lanes 0..7 of step W, the G2 line walk, beside step F
+            const uint32_t w0 = q_lds32(s_trace + 8u * (unsigned)t), w1 = q_lds32(s_trace + 8u * (unsigned)t + 4u);
+            uint32_t sid = w0 & 0xffu, ln = vlane;
+            const uint32_t sw = (w0 >> 8) & 0xffu;
+            if (sw != 0xffu && vlane >= BN_COOP4_W_LANE0) { sid = sw; ln = vlane - BN_COOP4_W_LANE0; }
+            if (sid != 0xffu) coop4_step(sid | (w1 & 0xffffff00u), s_code, s_hdr, wbase, ln, part);
             coop4_sync(group);
         }
     }
@@ -237,13 +254,13 @@ __global__ void __launch_bounds__(BN_COOP4_MAX_GROUPS * BN_COOP4_GROUP, 1) k_coo
 // Gt::pow on a group (k_coop_gt_pow of bn_coop.cuh, same walk over the canonical scalar)
 __global__ void __launch_bounds__(BN_COOP4_MAX_GROUPS * BN_COOP4_GROUP, 1) k_coop4_gt_pow(const Fq12* __restrict__ a, const Fq* __restrict__ fr,
                                                                                          Fq12* __restrict__ out, size_t n) {
-    const sp tab = coop_load_tables();
-    const sp s_code = tab, s_hdr = tab + 4u * BN_COOP_CODE_WORDS;
+    const sp tab = coop4_load_tables();
+    const sp s_code = tab, s_hdr = tab + 4u * BN_COOP4_CODE_WORDS;
     const unsigned group = threadIdx.x / BN_COOP4_GROUP, gt = threadIdx.x % BN_COOP4_GROUP;
     const unsigned vlane = ((((gt >> 5) + group) & 3u) << 3) | ((gt >> 2) & 7u), part = gt & 3u;   // lanes 0..7 (the busiest) of the block's groups on different sub-partitions
     const size_t i = (size_t)blockIdx.x * (blockDim.x / BN_COOP4_GROUP) + group;
     if (i >= n) return;
-    const sp wbase = tab + 4u * BN_COOP_TABLE_WORDS + group * BN_COOP_SLOT_BYTES;
+    const sp wbase = tab + 4u * BN_COOP4_TABLE_WORDS + group * BN_COOP_SLOT_BYTES;
     for (unsigned k = gt; k < BN_COOP_NCONST * 16u; k += BN_COOP4_GROUP) q_sts32(wbase + 4u * k, bn_coop_const[k]);
     const uint32_t* src = reinterpret_cast<const uint32_t*>(a + i);
     for (unsigned k = gt; k < 96u; k += BN_COOP4_GROUP) q_sts32(wbase + 64u * BN_COOP_SLOT_EREG1 + 4u * k, src[k]);

@@ -29,6 +29,22 @@ def test_miller_and_pairing_match_the_oracle():
     assert g.simulate(o.G1_ONE, o.G2_ONE) == o.pairing(o.G1_ONE, o.G2_ONE)
 
 
+def test_paired_program_of_the_quad_lane_executor():
+    """The line walk on lanes 24..31 beside the squarings / line multiplications on lanes 0..23 (one stage ahead, lines through
+    four buffers): same Miller value and pairing as the oracle, from the routines (with the cross-half hazard check: neither
+    half of a paired step reads or writes what the other writes) and from the ENCODED two-word trace."""
+    p, q = _pair()
+    pa, qa = o.g_to_affine(o.FQ_OPS, p), o.g_to_affine(o.FQ2_OPS, q)
+    assert g.simulate_paired(p, q, "miller") == o.miller_loop(o.g2_precompute(qa), pa)
+    assert g.simulate_paired(p, q) == o.pairing(p, q) == g.decode_and_run_paired(p, q)
+    assert g.simulate_paired(o.G1_ONE, o.G2_ONE) == o.pairing(o.G1_ONE, o.G2_ONE)
+    steps, trace, marks, nseq = g.flatten4()
+    seq_steps, seq_trace, _ = g.flatten()
+    assert len(trace) < 0.66 * len(seq_trace)                     # 1,072 entries against 1,651 steps
+    assert all(s < nseq for s, _, _, _ in seq_trace)              # the one-warp executor loads a prefix of the step table
+    assert all(len(steps[sw].lanes) <= 8 and (sf is None or len(steps[sf].lanes) <= 24) for sf, sw, _, _, _ in trace if sw is not None)
+
+
 def test_final_exponentiation_phase_alone():
     p, q = _pair()
     f = g.simulate(p, q, "miller")

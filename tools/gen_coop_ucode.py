@@ -421,7 +421,89 @@ def build_routines():
     r.mul(fq6_products(t_(0), a[0:3], u) + fq6_products(t_(6), a[3:6], u))
     o0, o1 = fq6_outputs(t_(0)), fq6_outputs(t_(6))
     r.lin([(D + i, o0[i]) for i in range(3)] + [(D + 3 + i, [neg(t) for t in o1[i]]) for i in range(3)])
+    build_paired_routines(new, R)
     return R
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# paired routines of the quad-lane executor (csrc/bn_coop4.cuh): the G2 line walk on lanes 24..31 (one warp of the group) WHILE
+# lanes 0..23 square f and multiply the previous lines into it.  The walk never reads f, so it runs one stage ahead; lines cross
+# over through four buffers (two per stage, stages alternate).  During the Miller loop the Fq12 registers of the final
+# exponentiation are idle: the walk's temporaries and the line buffers live there.  Appended AFTER the routines above, so the
+# step numbers of the one-warp executor do not move.
+# ------------------------------------------------------------------------------------------------------------------
+def w_(i):
+    """temporaries of the walk"""
+    assert 0 <= i < 24
+    return S(E_BASE + i)
+
+
+YP, YN = S(E_BASE + 24), S(E_BASE + 25)      # the running point's Y as YP - YN (saves the walk a LIN step per doubling)
+T0 = S(E_BASE + 26)                          # z0 + xi z5 of the CURRENT f (first operand sum of the next squaring), by LINEB
+LINE_BUF = [E_BASE + 30 + 3 * j for j in range(4)]     # (ell_0, ell_vv P.x, ell_vw P.y) x [stage parity][doubling, addition]
+PAIRED_W_LANES, PAIRED_F_LANES = 8, 24
+
+
+def build_paired_routines(new, R):
+    ry = [T(YP), T(YN, -1)]
+    # ---- WINIT: the walk starts at R = (Q.x, Q.y, 1) with Y = YP - YN
+    r = new("WINIT")
+    r.lin([(YP, QA + 1), (YN, ZERO)])
+
+    # ---- WDBL: doubling step (src/groups/mod.rs:754-776) + the two scalings of src/groups/mod.rs:589; the line goes to base D
+    r = new("WDBL")
+    r.mul([(w_(0), RX, ry), (w_(1), [RX, RX, RX], RX), (w_(2), ry, ry), (w_(3), RZ, RZ), (w_(4), ry + [T(RZ)], ry + [T(RZ)])])
+    h = [T(w_(4)), T(w_(2), -1), T(w_(3), -1)]                                   # h = (Y + Z)^2 - b - c
+    r.mul([(w_(7), C_B3, w_(3)),                                                 # e = 3 b' Z^2
+           (D + 1, w_(1), PA),                                                   # ell_vv P.x, ell_vv = 3 X^2
+           (D + 2, [neg(t) for t in h], PA + 1),                                 # ell_vw P.y, ell_vw = -h
+           (RZ, w_(2), h)])                                                      # Z' = b h
+    r.lin([(D + 0, [T(w_(7), 1, 1), T(w_(2), -1, 1)]),                           # ell_0 = xi (e - b)
+           (w_(5), w_(0), True),                                                 # a = X Y / 2
+           (w_(8), [T(w_(2))] + times(T(w_(7)), 3), True)])                      # g = (b + 3 e) / 2
+    r.mul([(RX, w_(5), [T(w_(2))] + times(T(w_(7), -1), 3)),                     # X' = a (b - 3 e)
+           (YP, w_(8), w_(8)), (YN, [w_(7), w_(7), w_(7)], w_(7))])              # Y' = g^2 - 3 e^2
+
+    # ---- WADD: mixed addition step (src/groups/mod.rs:731-752) with the affine point at base B, line to base D
+    r = new("WADD")
+    bx, by = B, B + 1
+    r.mul([(w_(10), RZ, bx), (w_(11), RZ, by)])
+    d = [T(RX), T(w_(10), -1)]                                                   # d = X - Z x
+    e = ry + [T(w_(11), -1)]                                                     # e = Y - Z y
+    r.mul([(w_(12), d, d), (w_(13), e, e), (w_(14), e, bx), (w_(15), d, by),     # f, g, e x, d y
+           (D + 1, [neg(t) for t in e], PA), (D + 2, d, PA + 1)])                # ell_vv = -e, ell_vw = d, scaled
+    r.mul([(w_(16), d, w_(12)), (w_(17), RX, w_(12)), (w_(18), RZ, w_(13))])     # h, i, Z g
+    r.lin([(w_(19), [T(w_(18)), T(w_(16))] + times(T(w_(17), -1), 2)),           # j = Z g + h - 2 i
+           (w_(20), times(T(w_(17)), 3) + [T(w_(18), -1), T(w_(16), -1)]),       # i - j
+           (D + 0, [T(w_(14), 1, 1), T(w_(15), -1, 1)])])                        # ell_0 = xi (e x - d y)
+    r.mul([(w_(21), d, w_(19)), (w_(22), e, w_(20)), (w_(23), w_(16), ry), (RZ, RZ, w_(16))])
+    r.lin([(RX, w_(21)), (YP, [T(w_(22)), T(w_(23), -1)]), (YN, ZERO)])
+
+    # ---- LINEB: f <- f * line with (x0, x2, x4) already scaled at base A; also T0 = z0 + xi z5 of the new f
+    r = new("LINEB")
+    z = [F + i for i in range(6)]
+    x0, x2, x4 = A + 0, A + 1, A + 2
+    prods = [(z[0], x0), (z[1], x2), (z[4], x4), (z[1], x0), (z[5], x4), (z[2], x2), (z[2], x0), (z[0], x2), (z[3], x4),
+             (z[3], x0), (z[2], x4), (z[4], x2), (z[4], x0), (z[0], x4), (z[5], x2), (z[5], x0), (z[3], x2), (z[1], x4)]
+    r.mul([(t_(i), a, b) for i, (a, b) in enumerate(prods)])
+    p = [T(t_(i)) for i in range(18)]
+    r.lin([(z[0], [p[0], xi(p[1]), xi(p[2])]), (z[1], [p[3], xi(p[4]), xi(p[5])]), (z[2], [p[6], p[7], p[8]]),
+           (z[3], [p[9], xi(p[10]), xi(p[11])]), (z[4], [p[12], p[13], xi(p[14])]), (z[5], [p[15], p[16], p[17]]),
+           (T0, [p[0], xi(p[1]), xi(p[2]), xi(p[15]), xi(p[16]), xi(p[17])])])
+
+    # ---- SQR12B: f <- f^2 (src/fields/fq12.rs:295-303) with a0 + v a1 taken as operand sums (T0 from LINEB): one LIN step less
+    r = new("SQR12B")
+    r.mul(fq6_products(t_(3), [z[0], z[1], z[2]], [z[3], z[4], z[5]]) +
+          fq6_products(t_(9), [[z[0], z[3]], [z[1], z[4]], [z[2], z[5]]], [T0, [z[1], z[3]], [z[2], z[4]]]))
+    oa, ot = fq6_outputs(t_(3)), fq6_outputs(t_(9))
+    r.lin([(t_(15 + i), oa[i]) for i in range(3)] + [(t_(18 + i), ot[i]) for i in range(3)])
+    ab, tt = [T(t_(15 + i)) for i in range(3)], [T(t_(18 + i)) for i in range(3)]
+    r.lin([(z[0], [tt[0], neg(ab[0]), xi(neg(ab[2]))]), (z[1], [tt[1], neg(ab[1]), neg(ab[0])]), (z[2], [tt[2], neg(ab[2]), neg(ab[1])]),
+           (z[3], times(ab[0], 2)), (z[4], times(ab[1], 2)), (z[5], times(ab[2], 2))])
+    for name in ("WINIT", "WDBL", "WADD"):
+        assert all(len(st.lanes) <= PAIRED_W_LANES for st in R[name].steps), name
+    for name in ("LINEB", "SQR12B"):
+        assert all(len(st.lanes) <= PAIRED_F_LANES for st in R[name].steps), name
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -525,6 +607,108 @@ def build_program():
     marks["fexp_end"] = len(calls)
     marks["pairing_end"] = len(calls)
     return calls, marks
+
+
+def build_paired_miller():
+    """The Miller loop of the quad-lane executor as stages (f_calls, w_calls): f_calls = [(routine, base A)] run on lanes 0..23,
+    w_calls = [(routine, base D, base B)] on lanes 24..31 at the same time; a stage ends when both lists are done.  Walk stage k
+    (the line steps of NAF digit k; stages 64, 65: the additions of pi(Q), -pi^2(Q)) runs beside f stage k - 1."""
+    naf = o.ATE_LOOP_COUNT_NAF
+    walk = []                                   # per walk stage: [(routine, D, B)] and the buffers it fills
+    for k, dg in enumerate(naf):
+        par = k & 1
+        calls = [("WDBL", LINE_BUF[2 * par], 0)]
+        if dg:
+            calls.append(("WADD", LINE_BUF[2 * par + 1], (QA if dg == 1 else QN).off))
+        walk.append(calls)
+    walk.append([("WADD", LINE_BUF[0], Q1.off)])                 # stage 64
+    walk.append([("WADD", LINE_BUF[2], Q2.off)])                 # stage 65
+    fch = []
+    for k in range(len(walk)):
+        calls = [("SQR12B", 0)] if 0 < k < 64 else []            # the reference squares 1 in the first iteration: same value
+        calls += [("LINEB", d) for _, d, _ in walk[k]]
+        fch.append(calls)
+    stages = [([], [("WINIT", 0, 0)] + walk[0])]
+    for k in range(len(walk)):
+        stages.append((fch[k], walk[k + 1] if k + 1 < len(walk) else []))
+    return stages
+
+
+def flatten_paired(R, index):
+    """Trace of the quad-lane executor: entries (step F or None, step W or None, D, A, B).  TOAFF and FROBQ first (all lanes),
+    then the paired Miller stages, then the final exponentiation (all lanes, the sequential program's calls)."""
+    calls, marks = build_program()
+    trace, tm = [], {}
+    tm["pairing_begin"] = 0
+    for name in ("TOAFF", "FROBQ"):
+        for k in range(len(R[name].steps)):
+            trace.append((index[(name, k)], None, 0, 0, 0))
+    for f_calls, w_calls in build_paired_miller():
+        fs = [(index[(n, k)], a) for n, a in f_calls for k in range(len(R[n].steps))]
+        ws = [(index[(n, k)], d, b) for n, d, b in w_calls for k in range(len(R[n].steps))]
+        for i in range(max(len(fs), len(ws))):
+            sf, a = fs[i] if i < len(fs) else (None, 0)
+            sw, d, b = ws[i] if i < len(ws) else (None, 0, 0)
+            trace.append((sf, sw, d, a, b))
+    tm["miller_end"] = tm["fexp_begin"] = len(trace)
+    for name, bd, ba, bb in calls[marks["fexp_begin"]:marks["fexp_end"]]:
+        for k in range(len(R[name].steps)):
+            trace.append((index[(name, k)], None, bd, ba, bb))
+    tm["fexp_end"] = tm["pairing_end"] = len(trace)
+    return trace, tm
+
+
+def run_paired_entry(slots, steps, entry):
+    """One trace entry of the quad-lane executor on the simulator: both steps read the slots as they were, then write."""
+    sf, sw, d, a, b = entry
+    bases = (d, a, b)
+    if sw is None:
+        run_step(slots, steps[sf], bases)
+        return
+    assert sf is None or len(steps[sf].lanes) <= PAIRED_F_LANES
+    assert len(steps[sw].lanes) <= PAIRED_W_LANES
+    before = list(slots)
+    merged = {}
+    touched = []
+    for sid in (sf, sw):
+        if sid is None:
+            continue
+        work = list(before)
+        run_step(work, steps[sid], bases)
+        reads = set()
+        for ln in steps[sid].lanes:
+            for k in ("a", "b", "t"):
+                for t in ln.get(k, []):
+                    reads.add(_resolve(t[0], bases))
+        writes = {i for i in range(len(work)) if work[i] is not before[i]}
+        writes |= {_resolve(ln["dst"], bases) for ln in steps[sid].lanes}
+        touched.append((reads, writes))
+        for i in writes:
+            assert i not in merged, "both halves of a paired step write slot %d" % i
+            merged[i] = work[i]
+    if len(touched) == 2:
+        (r0, w0), (r1, w1) = touched
+        assert not (w0 & r1) and not (w1 & r0), "one half of a paired step reads what the other writes: %s %s" % (w0 & r1, w1 & r0)
+    for i, v in merged.items():
+        slots[i] = v
+
+
+def simulate_paired(p, q, phase="pairing"):
+    """The quad-lane executor's program on Jacobian points (canonical integer tuples), from the routines."""
+    R = build_routines()
+    index, steps = {}, []
+    for name, r in R.items():
+        for k, st in enumerate(r.steps):
+            index[(name, k)] = len(steps)
+            steps.append(st)
+    trace, tm = flatten_paired(R, index)
+    slots = fresh_slots()
+    for i in range(3):
+        slots[IN_P.off + i] = (p[i] % Q, 0)
+        slots[IN_Q.off + i] = q[i]
+    for entry in trace[:tm["miller_end"] if phase == "miller" else tm["pairing_end"]]:
+        run_paired_entry(slots, steps, entry)
+    return get_f12(slots, F.off)
 
 
 def constants():
@@ -654,6 +838,31 @@ def flatten():
     return steps, trace, tmarks
 
 
+NONE_STEP = 0xff
+N_SEQ_ROUTINE = "WINIT"          # the first routine the one-warp executor never runs: its tables end there
+
+
+def flatten4():
+    """(steps, paired trace, marks, number of steps the one-warp executor needs)."""
+    R = build_routines()
+    index, steps = {}, []
+    for name, r in R.items():
+        for k, st in enumerate(r.steps):
+            index[(name, k)] = len(steps)
+            steps.append(st)
+    trace, tm = flatten_paired(R, index)
+    return steps, trace, tm, index[(N_SEQ_ROUTINE, 0)]
+
+
+def encode_paired(trace):
+    """Two words per entry: step F | step W << 8 (0xff = none), then base D << 8 | base A << 16 | base B << 24."""
+    words = []
+    for sf, sw, d, a, b in trace:
+        words.append((NONE_STEP if sf is None else sf) | ((NONE_STEP if sw is None else sw) << 8))
+        words.append((d << 8) | (a << 16) | (b << 24))
+    return words
+
+
 def mont_limbs(v):
     m = v * o.MONT_R % Q
     return [(m >> (32 * i)) & 0xffffffff for i in range(8)]
@@ -700,6 +909,16 @@ def emit(path):
     arr("bn_coop_hdr", hdrs)
     arr("bn_coop_code", code, 16)
     arr("bn_coop_trace", [s | (bd << 8) | (ba << 16) | (bb << 24) for s, bd, ba, bb in trace])
+    # the quad-lane executor's trace (csrc/bn_coop4.cuh): paired steps, two words per entry
+    steps4, trace4, marks4, nseq = flatten4()
+    assert steps4 == steps or len(steps4) == len(steps)
+    assert all(ts[0] < nseq for ts in trace), "the one-warp executor's trace stays inside its prefix of the step table"
+    w("#define BN_COOP_NSTEPS_SEQ %d" % nseq)
+    w("#define BN_COOP4_NTRACE %d" % len(trace4))
+    for k in ("pairing_begin", "miller_end", "fexp_begin", "fexp_end", "pairing_end"):
+        w("#define BN_COOP4_T_%s %d" % (k.upper(), marks4[k]))
+    w("#define BN_COOP4_W_LANE0 %d" % PAIRED_F_LANES)
+    arr("bn_coop4_trace", encode_paired(trace4))
     cs = constants()
     vals = []
     for k in range(N_CONST):
@@ -758,6 +977,63 @@ def decode_and_run(p, q):
     return get_f12(slots, F.off)
 
 
+def decode_and_run_paired(p, q):
+    """The quad-lane executor's view of the ENCODED tables: per entry, lanes 24..31 take lanes 0..7 of step W when there is one,
+    the other lanes (all 32 without a step W) take step F; reads see the slots as they were before the entry."""
+    steps, trace, marks, _ = flatten4()
+    enc = [encode_step(st) for st in steps]
+    tw = encode_paired(trace)
+    slots = fresh_slots()
+    for i in range(3):
+        slots[IN_P.off + i] = (p[i] % Q, 0)
+        slots[IN_Q.off + i] = q[i]
+    half_inv = pow(2, -1, Q)
+    for e in range(marks["pairing_begin"], marks["pairing_end"]):
+        w0, w1 = tw[2 * e], tw[2 * e + 1]
+        sf, sw = w0 & 0xff, (w0 >> 8) & 0xff
+        bases = (0, (w1 >> 8) & 0xff, (w1 >> 16) & 0xff, (w1 >> 24) & 0xff)
+        writes = []
+        for lane in range(32):
+            if sw != NONE_STEP and lane >= PAIRED_F_LANES:
+                sid, ln = sw, lane - PAIRED_F_LANES
+            else:
+                sid, ln = sf, lane
+            if sid == NONE_STEP:
+                continue
+            h, words = enc[sid]
+            op, n0, n1 = h & 15, (h >> 4) & 15, (h >> 8) & 15
+            lw = words[0][ln]
+            if not (lw >> 10) & 1:
+                continue
+            tl = []
+            for k in range(4):
+                tl += [words[1 + k][ln] & 0xffff, words[1 + k][ln] >> 16]
+
+            def acc(ts):
+                a = (0, 0)
+                for t in ts:
+                    v = slots[(t & 0xff) + bases[(t >> 8) & 3]]
+                    a = o.fq2_sub(a, v) if (t >> 10) & 1 else o.fq2_add(a, v)
+                return a
+            x, y = acc(tl[:n0]), acc(tl[n0:n0 + n1])
+            if op == OP_MUL:
+                if (lw >> 11) & 1:
+                    x = _conj(x)
+                if (lw >> 12) & 1:
+                    y = _conj(y)
+                r = o.fq2_mul(x, y)
+            elif op == OP_LIN:
+                r = o.fq2_add(x, o.fq2_mul_by_nonresidue(y))
+                if (lw >> 13) & 1:
+                    r = (r[0] * half_inv % Q, r[1] * half_inv % Q)
+            else:
+                r = (pow(x[0], Q - 2, Q), 0)
+            writes.append(((lw & 0xff) + bases[(lw >> 8) & 3], r))
+        for d, r in writes:
+            slots[d] = r
+    return get_f12(slots, F.off)
+
+
 if __name__ == "__main__":
     import random
     if "--check" in sys.argv:
@@ -765,8 +1041,8 @@ if __name__ == "__main__":
         for _ in range(3):
             p = o.g_mul(o.FQ_OPS, o.G1_ONE, rng.randrange(1, o.R_ORDER))
             q = o.g_mul(o.FQ2_OPS, o.G2_ONE, rng.randrange(1, o.R_ORDER))
-            assert simulate(p, q) == o.pairing(p, q) == decode_and_run(p, q)
+            assert simulate(p, q) == o.pairing(p, q) == decode_and_run(p, q) == simulate_paired(p, q) == decode_and_run_paired(p, q)
         print("microcode matches the oracle")
     else:
         n = emit(os.path.join(ROOT, "paritytech-bn_b200", "csrc", "bn_coop_ucode.cuh"))
-        print("wrote bn_coop_ucode.cuh: %d steps, %d executed per pairing" % n)
+        print("wrote bn_coop_ucode.cuh: %d steps, %d executed per pairing on one warp, %d on four" % (n + (len(flatten4()[1]),)))
