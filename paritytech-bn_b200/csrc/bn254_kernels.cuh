@@ -43,7 +43,7 @@ __device__ __noinline__ bool pair_to_affine(AffG1& pa, AffG2& qa, const G1& p, c
     fq_mul(t, q.z.c1, q.z.c1);
     fq_add(n, n, t);                 // norm(q.z) != 0
     fq_mul_ni(t, p.z, n);
-    fq_inv_eea(ti, t);                // binary extended Euclid: a third of the Fermat power's pipe time, same element
+    fq_inv_bgcd(ti, t);               // binary extended Euclid in 17 rounds of 30 approximated steps: same element
     fq_mul_ni(pzi, ti, n);           // 1/p.z
     fq_mul_ni(ni, ti, p.z);          // 1/norm
     fq_mul_ni(z2, pzi, pzi);
@@ -772,10 +772,12 @@ BN_KERNEL k_field_op(int op, const uint4* __restrict__ a, const uint4* __restric
     switch (op) {
         case 0: case 1: case 2: case 9: {
             Fq x = reinterpret_cast<const Fq*>(a)[i], r;
-            if (op == 9) {   // both inversions must agree: Fermat power and the uniform binary extended Euclid (all-ones if not)
-                Fq r2, r3;
+            if (op == 9) {   // all inversions must agree: Fermat power, its window, the uniform binary extended Euclid and its
+                             // 30-step rounds, which must also end on their own (status 1, or 0 for zero) -- all-ones if not
+                Fq r2, r3, r4;
                 fq_inv(r, x); fq_inv_eea(r2, x); fq_inv_w4(r3, x);
-                if (!fq_eq(r, r2) || !fq_eq(r, r3)) { for (int k = 0; k < 8; k++) r.v[k] = 0xffffffffu; }
+                const int st = fq_inv_bgcd_core(r4, x);
+                if (!fq_eq(r, r2) || !fq_eq(r, r3) || !fq_eq(r, r4) || st == 2) { for (int k = 0; k < 8; k++) r.v[k] = 0xffffffffu; }
             }
             else {
                 Fq y = reinterpret_cast<const Fq*>(b)[i];

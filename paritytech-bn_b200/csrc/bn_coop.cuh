@@ -125,7 +125,7 @@ __device__ __forceinline__ void coop_step(uint32_t tr, sp s_code, sp s_hdr, sp w
         }
     } else {                                                     // INV: one lane
         r.c0 = fq_zero(); r.c1 = fq_zero();
-        if (active) fq_inv_eea(r.c0, x.c0);
+        if (active) fq_inv_bgcd(r.c0, x.c0);
     }
     if (active) {
         const uint32_t slot = (w0 & 0xffu) + ((bases >> (8u * ((w0 >> 8) & 3u))) & 0xffu);

@@ -160,7 +160,7 @@ __device__ __forceinline__ void coop4_step(uint32_t tr, sp s_code, sp s_hdr, sp 
             }
             Fq x, r;
             acc9_reduce<false>(x, ax);
-            fq_inv_eea(r, x);
+            fq_inv_bgcd(r, x);
             q_st_fq(dst, r);
             q_st_fq(dst + 32u, fq_zero());
         }

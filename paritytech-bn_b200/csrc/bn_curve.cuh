@@ -16,7 +16,7 @@ struct FqOps {
     static BN_HD void neg(T& r, const T& a) { fq_neg(r, a); }
     static BN_HD void mul(T& r, const T& a, const T& b) { fq_mul_ni(r, a, b); }
     static BN_HD void sqr(T& r, const T& a) { fq_mul_ni(r, a, a); }
-    static BN_HD bool inv(T& r, const T& a) { return fq_inv_eea(r, a); }
+    static BN_HD bool inv(T& r, const T& a) { return fq_inv_bgcd(r, a); }
     static BN_HD bool is_zero(const T& a) { return fq_is_zero(a); }
     static BN_HD bool eq(const T& a, const T& b) { return fq_eq(a, b); }
     static BN_HD T zero() { return fq_zero(); }

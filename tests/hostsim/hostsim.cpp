@@ -53,6 +53,9 @@ extern "C" void hs_fq_inv(const void* a, void* o, unsigned char* some, size_t n)
 extern "C" void hs_fq_inv_eea(const void* a, void* o, unsigned char* some, size_t n) {
     for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r; some[i] = fq_inv_eea(r, x); st(o, i, r); }
 }
+extern "C" void hs_fq_inv_bgcd(const void* a, void* o, unsigned char* some, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r; some[i] = (unsigned char)fq_inv_bgcd_core(r, x); st(o, i, r); }   // 2 = fallback needed
+}
 extern "C" void hs_fq_inv_w4(const void* a, void* o, unsigned char* some, size_t n) {
     for (size_t i = 0; i < n; i++) { Fq x = ld<Fq>(a, i), r; some[i] = fq_inv_w4(r, x); st(o, i, r); }
 }

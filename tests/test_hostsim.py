@@ -89,6 +89,20 @@ def test_inversions_and_frobenius():
             assert some[i] == 0 and got == 0
         else:       # image v = a R  ->  image of the inverse = a^-1 R = R^2 / v
             assert some[i] == 1 and got == pow(v, -1, o.Q) * o.MONT_R * o.MONT_R % o.Q, i
+    # the same inverse in 17 rounds of 30 approximated steps (fq_inv_bgcd): status 1 everywhere, i.e. the plain loop is never needed
+    vals += [rng.randrange(1, 1 << rng.randrange(1, 254)) for _ in range(3000)] + [o.Q - rng.randrange(1, 1 << rng.randrange(1, 250)) for _ in range(3000)]
+    vals += [(1 << k) + d for k in range(1, 254) for d in (-1, 0, 1) if 0 < (1 << k) + d < o.Q]
+    vals += [rng.randrange(o.Q) for _ in range(20000)]
+    a = np.frombuffer(b"".join(v.to_bytes(32, "little") for v in vals), dtype=np.uint8).copy()
+    out, some = np.empty_like(a), np.empty(len(vals), dtype=np.uint8)
+    hostsim.lib().hs_fq_inv_bgcd(_p(a), _p(out), _p(some), ctypes.c_size_t(len(vals)))
+    r2 = o.MONT_R * o.MONT_R % o.Q
+    for i, v in enumerate(vals):
+        got = int.from_bytes(out[32 * i:32 * i + 32].tobytes(), "little")
+        if v == 0:
+            assert some[i] == 0 and got == 0
+        else:
+            assert some[i] == 1 and got == pow(v, -1, o.Q) * r2 % o.Q, (i, hex(v), some[i])
     a = np.concatenate([rand_elems(12, 6), _b(o.FQ12_ZERO)])
     out = np.empty_like(a)
     some = np.empty(7, dtype=np.uint8)
