@@ -374,6 +374,18 @@ BN_HD void wide_add(FqWide& a, const FqWide& b) {  // a += b (caller guarantees 
     }
 #endif
 }
+BN_HD void wide_sub_nb(FqWide& a, const FqWide& b) {  // a -= b for a >= b (no add-back code)
+#if defined(__CUDA_ARCH__)
+    wide_sub_nb_ptx(a.v, b.v);
+#else
+    int64_t br = 0;
+    for (int i = 0; i < 16; i++) {
+        int64_t d = (int64_t)a.v[i] - b.v[i] + br;
+        a.v[i] = (uint32_t)d;
+        br = d >> 32;
+    }
+#endif
+}
 BN_HD void wide_sub(FqWide& a, const FqWide& b) {  // a -= b; on borrow add q*2^256 (stays in [0, qR))
 #if defined(__CUDA_ARCH__)
     wide_sub_ptx(a.v, b.v);

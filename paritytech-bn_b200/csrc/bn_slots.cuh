@@ -354,8 +354,8 @@ __device__ __noinline__ void s_dot3(Fq2& out, const Fq12& f, uint32_t zi, sp xba
         fq_mulwide(p, sa, sb); wide_add(s, p);
         z = zn;
     }
-    wide_sub(s, t0);                 // never borrows
-    wide_sub(s, t1);
+    wide_sub_nb(s, t0);                 // never borrows
+    wide_sub_nb(s, t1);
     wide_sub(t0, t1);                // + q 2^256 on borrow: in [0, q 2^256)
     Fq hi, zero = fq_zero();
 #pragma unroll

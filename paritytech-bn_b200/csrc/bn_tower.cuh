@@ -322,8 +322,8 @@ BN_HD void fq2_mul_inl(Fq2& r, const Fq2& a, const Fq2& b) {
     fq_add_noreduce(sa, a.c0, a.c1);
     fq_add_noreduce(sb, b.c0, b.c1);
     fq_mulwide(s, sa, sb);          // < 4q^2 < q*2^256
-    wide_sub(s, t0);                // >= 0: a0*b1 + a1*b0 + t1
-    wide_sub(s, t1);                // a0*b1 + a1*b0 < 2q^2
+    wide_sub_nb(s, t0);                // >= 0: a0*b1 + a1*b0 + t1
+    wide_sub_nb(s, t1);                // a0*b1 + a1*b0 < 2q^2
     wide_sub(t0, t1);               // a0*b0 - a1*b1 (+ q*2^256 if negative)
     fq_redc(r.c0, t0);
     fq_redc(r.c1, s);

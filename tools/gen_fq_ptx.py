@@ -490,6 +490,18 @@ def gen_wide_sub():
     return P
 
 
+def gen_wide_sub_nb():
+    """a -= b over 512 bits for a >= b (the two Karatsuba corrections of an Fq2 product never borrow): no add-back code."""
+    P = Prog("wide_sub_nb_ptx")
+    a = ["a%d" % i for i in range(16)]
+    b = ["b%d" % i for i in range(16)]
+    P.inputs = b
+    P.outputs = a
+    for i in range(16):
+        P.emit("sub.cc" if i == 0 else ("subc.cc" if i < 15 else "subc"), a[i], a[i], b[i])
+    return P
+
+
 # ------------------------------------------------------------------------------------------------
 def limbs(x, n):
     return [(x >> (32 * i)) & M32 for i in range(n)]
@@ -506,7 +518,7 @@ def check():
     edge = [0, 1, Q - 1, Q - 2, (1 << 253), R % Q, M32, Q >> 1]
     vals = edge + [rng.randrange(Q) for _ in range(300)]
     pm, pw, pr, pa, ps = gen_mul(), gen_mulwide(), gen_redc(), gen_add(), gen_sub()
-    pwa, pws = gen_wide_add(), gen_wide_sub()
+    pwa, pws, pwn = gen_wide_add(), gen_wide_sub(), gen_wide_sub_nb()
     n = 0
     for a in vals:
         for b in (vals if a in edge else rng.sample(vals, 12)):
@@ -542,6 +554,8 @@ def check():
         assert got == (t - u if t >= u else t - u + Q * R), "wide_sub"
         if t + u < (1 << 512):
             assert unl(pwa.run(env), pwa.outputs) == t + u, "wide_add"
+        if t >= u:
+            assert unl(pwn.run(env), pwn.outputs) == t - u, "wide_sub_nb"
     pp, pn = gen_lin9(False), gen_lin9(True)
     nl = 0
     # sweep the quotient estimate: 9a + b (and 9a + q - b) just below / at / above every multiple of q, plus random pairs
@@ -644,7 +658,7 @@ def main():
                 "// Outputs are early-clobber ('=&r'): they never alias an input register.\n"
                 "#pragma once\n#include <stdint.h>\n\n")
         for P, io in ((gen_mul(), False), (gen_mulwide(), False), (gen_redc(), False), (gen_add(), False), (gen_sub(), False), (gen_lin9(False), False), (gen_lin9(True), False), (gen_red9(), False),
-                      (gen_wide_add(), True), (gen_wide_sub(), True)):
+                      (gen_wide_add(), True), (gen_wide_sub(), True), (gen_wide_sub_nb(), True)):
             f.write(emit_function(P, io))
             f.write("\n")
     print("wrote", os.path.normpath(out))
