@@ -277,15 +277,17 @@ __global__ void __launch_bounds__(BN_COOP4_MAX_GROUPS * BN_COOP4_GROUP, 1) k_coo
     coop4_sync(group);
     bool started = false;
     const uint32_t mul_bases = ((uint32_t)BN_COOP_SLOT_F << 8) | ((uint32_t)BN_COOP_SLOT_F << 16) | ((uint32_t)BN_COOP_SLOT_EREG1 << 24);
+    // SQR12B takes a0 + v a1 of the accumulator from the slot T0, which SQR12B, MUL12T and T0INIT leave behind: one LIN step less
 #pragma unroll 1
     for (int b = 255; b >= 0; b--) {
-        if (started) coop4_call(BN_COOP_R_SQR12_BEGIN, BN_COOP_R_SQR12_COUNT, 0u, s_code, s_hdr, wbase, vlane, part, group);
+        if (started) coop4_call(BN_COOP_R_SQR12B_BEGIN, BN_COOP_R_SQR12B_COUNT, 0u, s_code, s_hdr, wbase, vlane, part, group);
         if ((e[b >> 5] >> (b & 31)) & 1u) {
             if (started) {
-                coop4_call(BN_COOP_R_MUL12_BEGIN, BN_COOP_R_MUL12_COUNT, mul_bases, s_code, s_hdr, wbase, vlane, part, group);
+                coop4_call(BN_COOP_R_MUL12T_BEGIN, BN_COOP_R_MUL12T_COUNT, mul_bases, s_code, s_hdr, wbase, vlane, part, group);
             } else {
                 if (gt < 24u) q_sts128(wbase + 64u * BN_COOP_SLOT_F + 16u * gt, q_lds128(wbase + 64u * BN_COOP_SLOT_EREG1 + 16u * gt));
                 coop4_sync(group);
+                coop4_call(BN_COOP_R_T0INIT_BEGIN, BN_COOP_R_T0INIT_COUNT, 0u, s_code, s_hdr, wbase, vlane, part, group);
                 started = true;
             }
         }

@@ -57,6 +57,7 @@ def test_pow_walk_with_in_place_routines():
     a = g.simulate(p, q)
     for k in (0, 1, 2, 0xb5, rng.randrange(1 << 70)):
         assert g.simulate_pow(a, k) == o.fq12_pow(a, k)
+        assert g.simulate_pow4(a, k) == o.fq12_pow(a, k)           # the quad-lane executor's SQR12B / MUL12T / T0INIT
 
 
 def test_encoded_tables_decode_to_the_same_result():

@@ -439,7 +439,7 @@ def w_(i):
 
 
 YP, YN = S(E_BASE + 24), S(E_BASE + 25)      # the running point's Y as YP - YN (saves the walk a LIN step per doubling)
-T0 = S(E_BASE + 26)                          # z0 + xi z5 of the CURRENT f (first operand sum of the next squaring), by LINEB
+T0 = TMP + 47                                # z0 + xi z5 of the CURRENT Fq12 accumulator (first operand sum of the next squaring)
 LINE_BUF = [E_BASE + 30 + 3 * j for j in range(4)]     # (ell_0, ell_vv P.x, ell_vw P.y) x [stage parity][doubling, addition]
 PAIRED_W_LANES, PAIRED_F_LANES = 8, 24
 
@@ -499,7 +499,22 @@ def build_paired_routines(new, R):
     r.lin([(t_(15 + i), oa[i]) for i in range(3)] + [(t_(18 + i), ot[i]) for i in range(3)])
     ab, tt = [T(t_(15 + i)) for i in range(3)], [T(t_(18 + i)) for i in range(3)]
     r.lin([(z[0], [tt[0], neg(ab[0]), xi(neg(ab[2]))]), (z[1], [tt[1], neg(ab[1]), neg(ab[0])]), (z[2], [tt[2], neg(ab[2]), neg(ab[1])]),
-           (z[3], times(ab[0], 2)), (z[4], times(ab[1], 2)), (z[5], times(ab[2], 2))])
+           (z[3], times(ab[0], 2)), (z[4], times(ab[1], 2)), (z[5], times(ab[2], 2)),
+           (T0, [tt[0], neg(ab[0]), xi(ab[2])])])                      # z0' + xi z5' (a squaring may follow directly: Gt::pow)
+    # ---- Gt::pow of the quad-lane executor (k_coop4_gt_pow): SQR12B on the accumulator in F, then MUL12T = MUL12 whose last
+    # LIN step also leaves T0 = d0 + xi d5 for the squaring that follows; T0INIT sets it for a value copied into F.
+    r = new("MUL12T")
+    a, b = [A + i for i in range(6)], [B + i for i in range(6)]
+    r.mul(fq6_products(t_(0), a[0:3], b[0:3]) + fq6_products(t_(6), a[3:6], b[3:6]) +
+          fq6_products(t_(12), [[a[i], a[3 + i]] for i in range(3)], [[b[i], b[3 + i]] for i in range(3)]))
+    outs = fq6_outputs(t_(0)) + fq6_outputs(t_(6)) + fq6_outputs(t_(12))
+    r.lin([(t_(18 + k), outs[k]) for k in range(9)])
+    aa, bb, cc = ([T(t_(18 + 3 * k + i)) for i in range(3)] for k in range(3))
+    r.lin([(D + 0, [aa[0], xi(bb[2])]), (D + 1, [aa[1], bb[0]]), (D + 2, [aa[2], bb[1]])] +
+          [(D + 3 + i, [cc[i], neg(aa[i]), neg(bb[i])]) for i in range(3)] +
+          [(T0, [aa[0], xi(cc[2]), xi(neg(aa[2]))])])                  # d0 + xi d5 = aa0 + xi bb2 + xi (cc2 - aa2 - bb2)
+    r = new("T0INIT")
+    r.lin([(T0, [T(F), T(F + 5, 1, 1)])])
     for name in ("WINIT", "WDBL", "WADD"):
         assert all(len(st.lanes) <= PAIRED_W_LANES for st in R[name].steps), name
     for name in ("LINEB", "SQR12B"):
@@ -773,6 +788,26 @@ def simulate_pow(a, k):
     return get_f12(slots, F.off)
 
 
+def simulate_pow4(a, k):
+    """Gt::pow the way k_coop4_gt_pow walks it: T0INIT after the copy of the base, then SQR12B / MUL12T."""
+    R = build_routines()
+    slots = fresh_slots()
+    put_f12(slots, ereg(1), a)
+    put_f12(slots, F.off, o.FQ12_ONE)
+    started = False
+    for i in range(255, -1, -1):
+        if started:
+            run_program(slots, R, [("SQR12B", 0, 0, 0)])
+        if (k >> i) & 1:
+            if started:
+                run_program(slots, R, [("MUL12T", F.off, F.off, ereg(1))])
+            else:
+                put_f12(slots, F.off, a)
+                run_program(slots, R, [("T0INIT", 0, 0, 0)])
+                started = True
+    return get_f12(slots, F.off)
+
+
 def simulate_fexp(x):
     R = build_routines()
     calls, marks = build_program()
@@ -889,7 +924,7 @@ def emit(path):
     R = build_routines()
     pos = 0
     for name, r in R.items():
-        if name in ("SQR12", "MUL12"):
+        if name in ("SQR12", "MUL12", "SQR12B", "MUL12T", "T0INIT"):
             w("#define BN_COOP_R_%s_BEGIN %d" % (name, pos))
             w("#define BN_COOP_R_%s_COUNT %d" % (name, len(r.steps)))
         pos += len(r.steps)
