@@ -605,6 +605,14 @@ static int pairing_many_host(bn254_ctx* ctx, const void* g1, const void* g2, voi
     // last one).  With K parts the later parts' inputs travel while the first computes; each part's 448-thread kernels occupy
     // 1/K of the SMs.  Every part but the last is a whole number of blocks.
     int K = ctx->opt.pipeline < 2 ? 2 : ctx->opt.pipeline > 4 ? 4 : ctx->opt.pipeline;
+    // Beyond one wave a part must itself be a full wave of 448-thread blocks: smaller parts run as 224-thread blocks, two kernels
+    // of different lanes share every SM and evict each other's code (2^17 pairs: 45.4 ms on four lanes against 42.3 ms on two,
+    // scripts/bench_single_call_lanes.py).  Within one wave (block size forced below) the parts take disjoint SMs.
+    const size_t wave = (size_t)ctx->sms * BN_FEXP_BLOCK;
+    if (n > wave) {
+        const size_t whole = n / ((size_t)1 << 16);
+        if ((size_t)K > whole) K = whole < 2 ? 2 : (int)whole;
+    }
     size_t part = (((n + K - 1) / K + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK) * BN_FEXP_BLOCK;
     size_t lo[4], cnt[4], woff[4], wsz[4], wtot = 0;
     int parts = 0;
