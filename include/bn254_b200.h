@@ -75,7 +75,8 @@ typedef struct bn254_g2precomp bn254_g2precomp; /* device-resident G2Precomp tab
 typedef struct bn254_ctx_options {
     uint32_t struct_size;  /* sizeof(bn254_ctx_options) of the caller's header (forward compatibility) */
     int32_t pipeline;      /* BN254_PIPELINE      host-buffer pairing path: 0 = one batch; 1 or 2 = two part batches on two streams
-                              (copies overlap kernels); 3, 4 (default 4) = that many parts */
+                              (copies overlap kernels); 3 .. 8 (default 4) = that many parts; beyond one wave of 448-thread
+                              blocks the count is capped so that every part is itself a full wave */
     int32_t big_blocks;    /* BN254_BIG_BLOCKS    1: 512-thread blocks when they save waves; 2: for every batch > 512 (tests) */
     int32_t fused_miller;  /* BN254_FUSED_MILLER  0: affine -> line table -> Miller from table; 1: one fused kernel (A/B) */
     int32_t split_fexp;    /* BN254_SPLIT_FEXP    with fexp_smem = 0: 1 = easy + hard kernels, 0 = one kernel */

@@ -42,14 +42,15 @@ struct Arena {
     size_t bytes = 0;
 };
 
+#define BN_MAX_LANES 8   /* part batches of the pipelined host-buffer pairing path */
 struct bn254_ctx {
     int device = 0;
     int sms = 148;     // multiprocessor count (the phase-synchronised kernels run one block per SM)
     cudaStream_t stream = nullptr;    // all work of the context; outranks stream2
     cudaStream_t stream2 = nullptr;   // second lane of the pipelined host-buffer pairing path
-    cudaStream_t stream34[2] = {nullptr, nullptr};   // lanes 3 and 4 (pipeline = 3 / 4)
+    cudaStream_t stream34[BN_MAX_LANES - 2] = {};   // lanes 3 .. 8 (pipeline = 3 .. 8)
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_done = nullptr;
-    cudaEvent_t ev_join34[2] = {nullptr, nullptr};
+    cudaEvent_t ev_join34[BN_MAX_LANES - 2] = {};
     std::atomic<uint64_t> launches{0};
     Arena io;          // device copies of the host-pointer entry points' arguments and results
     Arena ws;          // kernel workspace: line-coefficient tables of the split Miller path, easy-part values
@@ -172,7 +173,7 @@ static int arena_reserve(bn254_ctx* ctx, Arena& a, size_t bytes, const char* wha
     if (a.p) {
         CU(cudaStreamSynchronize(ctx->stream));
         CU(cudaStreamSynchronize(ctx->stream2));
-        for (int k = 0; k < 2; k++) if (ctx->stream34[k]) CU(cudaStreamSynchronize(ctx->stream34[k]));
+        for (int k = 0; k < BN_MAX_LANES - 2; k++) if (ctx->stream34[k]) CU(cudaStreamSynchronize(ctx->stream34[k]));
         cudaFree(a.p);
         a.p = nullptr; a.bytes = 0;
     }
@@ -241,7 +242,7 @@ void bn254_ctx_destroy(bn254_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
     if (ctx->stream2) { cudaStreamSynchronize(ctx->stream2); cudaStreamDestroy(ctx->stream2); }
-    for (int k = 0; k < 2; k++) {
+    for (int k = 0; k < BN_MAX_LANES - 2; k++) {
         if (ctx->stream34[k]) { cudaStreamSynchronize(ctx->stream34[k]); cudaStreamDestroy(ctx->stream34[k]); }
         if (ctx->ev_join34[k]) cudaEventDestroy(ctx->ev_join34[k]);
     }
@@ -292,7 +293,7 @@ static int ctx_init(bn254_ctx* c, int device, const bn254_ctx_options* user) {
     cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
     CU(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_greatest));
     CU(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prio_least));
-    for (int k = 0; k < 2; k++) {
+    for (int k = 0; k < BN_MAX_LANES - 2; k++) {
         CU(cudaStreamCreateWithPriority(&c->stream34[k], cudaStreamNonBlocking, prio_least));
         CU(cudaEventCreateWithFlags(&c->ev_join34[k], cudaEventDisableTiming));
     }
@@ -604,7 +605,7 @@ static int pairing_many_host(bn254_ctx* ctx, const void* g1, const void* g2, voi
     // blocks together, so a single batch exposes both transfers completely (inputs before the first kernel, results after the
     // last one).  With K parts the later parts' inputs travel while the first computes; each part's 448-thread kernels occupy
     // 1/K of the SMs.  Every part but the last is a whole number of blocks.
-    int K = ctx->opt.pipeline < 2 ? 2 : ctx->opt.pipeline > 4 ? 4 : ctx->opt.pipeline;
+    int K = ctx->opt.pipeline < 2 ? 2 : ctx->opt.pipeline > BN_MAX_LANES ? BN_MAX_LANES : ctx->opt.pipeline;
     // Beyond one wave a part must itself be a full wave of 448-thread blocks: smaller parts run as 224-thread blocks, two kernels
     // of different lanes share every SM and evict each other's code (2^17 pairs: 45.4 ms on four lanes against 42.3 ms on two,
     // scripts/bench_single_call_lanes.py).  Within one wave (block size forced below) the parts take disjoint SMs.
@@ -614,7 +615,7 @@ static int pairing_many_host(bn254_ctx* ctx, const void* g1, const void* g2, voi
         if ((size_t)K > whole) K = whole < 2 ? 2 : (int)whole;
     }
     size_t part = (((n + K - 1) / K + BN_FEXP_BLOCK - 1) / BN_FEXP_BLOCK) * BN_FEXP_BLOCK;
-    size_t lo[4], cnt[4], woff[4], wsz[4], wtot = 0;
+    size_t lo[BN_MAX_LANES], cnt[BN_MAX_LANES], woff[BN_MAX_LANES], wsz[BN_MAX_LANES], wtot = 0;
     int parts = 0;
     for (size_t at = 0; at < n && parts < K; parts++) {
         size_t m = (parts == K - 1 || n - at < part) ? n - at : part;
@@ -628,8 +629,9 @@ static int pairing_many_host(bn254_ctx* ctx, const void* g1, const void* g2, voi
     // one-wave batches: each part on its own SMs with full blocks (smaller blocks sharing an SM would interleave their phases);
     // larger batches fill every SM with one block at a time anyway and keep the block size rule of sync_block
     unsigned fb = n <= (size_t)ctx->sms * BN_FEXP_BLOCK ? BN_FEXP_BLOCK : 0;
-    cudaStream_t lanes[4] = {ctx->stream, ctx->stream2, ctx->stream34[0], ctx->stream34[1]};
-    cudaEvent_t joins[4] = {nullptr, ctx->ev_join, ctx->ev_join34[0], ctx->ev_join34[1]};
+    cudaStream_t lanes[BN_MAX_LANES] = {ctx->stream, ctx->stream2};
+    cudaEvent_t joins[BN_MAX_LANES] = {nullptr, ctx->ev_join};
+    for (int k = 2; k < BN_MAX_LANES; k++) { lanes[k] = ctx->stream34[k - 2]; joins[k] = ctx->ev_join34[k - 2]; }
     CU(cudaEventRecord(ctx->ev_fork, ctx->stream));
     for (int k = 1; k < parts; k++) CU(cudaStreamWaitEvent(lanes[k], ctx->ev_fork, 0));
     int rc = 0;
