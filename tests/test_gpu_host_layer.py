@@ -158,20 +158,20 @@ def test_steady_state_calls_do_not_allocate(eng):
 
 
 def test_pipeline_lane_counts_give_identical_bytes():
-    """bn254_pairing_many splits a host batch of >= 2^16 pairs into 2, 3 or 4 part batches on as many streams (option
+    """bn254_pairing_many splits a host batch of >= 2^16 pairs into 2 .. 8 part batches on as many streams (option
     `pipeline`); every split, pageable or pinned output, must return the bytes of the single-batch path.  Ragged n: the last
     part is not a whole number of blocks."""
     import torch
 
     import paritytech_bn_b200 as bn
-    n, base = (1 << 16) + 1237, 256
+    n, base = (1 << 16) + 700, 256           # one wave (148 x 448 = 66,304): every requested part count is honoured
     p1, p2 = _pairs(base, 861)
     idx = np.arange(n) % base
     g1 = p1.reshape(base, G1)[idx].reshape(-1).copy(); g2 = p2.reshape(base, G2)[(idx * 5 + 2) % base].reshape(-1).copy()
     exp = c.pairing_many(g1[:base * G1], g2[:base * G2])
     ref = None
     pinned = torch.empty(n * GT, dtype=torch.uint8, pin_memory=True).numpy()
-    for lanes in (0, 2, 3, 4):
+    for lanes in (0, 2, 3, 4, 7, 8):
         e = bn.Engine(0, pipeline=lanes)
         try:
             got = e.pairing(g1, g2)
