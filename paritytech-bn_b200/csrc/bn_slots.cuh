@@ -155,19 +155,20 @@ __device__ __forceinline__ void fq2_3t2z(Fq2& out, const Fq2& t, const Fq2& z, b
     fq_dbl(d.c0, d.c0); fq_dbl(d.c1, d.c1);
     fq_add(out.c0, d.c0, t.c0); fq_add(out.c1, d.c1, t.c1);
 }
-// post: with S = (a + b)(a + xi b) and TMP = a b in the slots: ta = S - TMP - xi TMP, tb = 2 TMP (times xi if xi_d);
-// out_c = 3 ta - 2 zc, out_d = 3 tb + 2 zd written to local memory
+// post: with S = (a + b)(a + xi b) and TMP = a b in the slots: ta = S - TMP - xi TMP (ta0 = S0 - 10 m0 + m1, ta1 = S1 - 10 m1 - m0),
+// tb = 2 TMP (times xi if xi_d); out_c = 3 ta - 2 zc, out_d = 3 tb + 2 zd written to local memory
 __device__ __noinline__ void s_cyc_post(Fq2& out_c, Fq2& out_d, const Fq2& zc, const Fq2& zd, sp base, bool xi_d) {
     Fq2 z = fq2_ld(zc), w = fq2_ld(zd);                      // both old coefficients up front: one local-memory latency
     Fq2 m = s_ld(base + 128), s = s_ld(base + 192), u;
-    fq_lin9<true>(u.c0, m.c0, m.c1);
-    fq_lin9<false>(u.c1, m.c1, m.c0);
-    fq_sub(s.c0, s.c0, m.c0); fq_sub(s.c1, s.c1, m.c1);
-    fq_sub(s.c0, s.c0, u.c0); fq_sub(s.c1, s.c1, u.c1);      // ta
-    fq2_3t2z(z, s, z, false);
-    fq2_st(out_c, z);
-    if (xi_d) { fq_dbl(m.c0, u.c0); fq_dbl(m.c1, u.c1); }    // xi (2 TMP) = 2 (xi TMP)
-    else { fq_dbl(m.c0, m.c0); fq_dbl(m.c1, m.c1); }         // tb
+    Fq2 oc;
+    cyc_outc(oc.c0, s.c0, m.c0, m.c1, true, z.c0);
+    cyc_outc(oc.c1, s.c1, m.c1, m.c0, false, z.c1);
+    fq2_st(out_c, oc);
+    if (xi_d) {
+        fq_lin9<true>(u.c0, m.c0, m.c1);
+        fq_lin9<false>(u.c1, m.c1, m.c0);
+        fq_dbl(m.c0, u.c0); fq_dbl(m.c1, u.c1);              // xi (2 TMP) = 2 (xi TMP)
+    } else { fq_dbl(m.c0, m.c0); fq_dbl(m.c1, m.c1); }       // tb
     fq2_3t2z(w, m, w, true);
     fq2_st(out_d, w);
 }

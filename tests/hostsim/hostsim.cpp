@@ -40,6 +40,11 @@ extern "C" void hs_acc9_sum(const void* terms, unsigned nterms, unsigned signs, 
     st(o, 0, r);
 }
 
+// one component of the cyclotomic squaring's out_c (bn_slots.cuh s_cyc_post): 3 (s +- mx - 10 m) - 2 z
+extern "C" void hs_cyc_outc(const void* s, const void* m, const void* mx, int plus, const void* z, void* o, size_t n) {
+    for (size_t i = 0; i < n; i++) { Fq r; cyc_outc(r, ld<Fq>(s, i), ld<Fq>(m, i), ld<Fq>(mx, i), plus != 0, ld<Fq>(z, i)); st(o, i, r); }
+}
+
 UN(g1_neg, G1, jac_neg) UN(g2_neg, G2, jac_neg)
 extern "C" void hs_g1_eq(const void* a, const void* b, unsigned char* eq, size_t n) {
     for (size_t i = 0; i < n; i++) { G1 x = ld<G1>(a, i), y = ld<G1>(b, i); eq[i] = jac_eq(x, y); }

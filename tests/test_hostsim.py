@@ -379,3 +379,19 @@ def test_lazy_sums_of_the_quad_lane_executor():
         n = rng.randrange(0, 9)
         nx = rng.randrange(0, 9 - n)
         run([rfq() for _ in range(n)], rng.randrange(1 << n) if n else 0, [rfq() for _ in range(nx)], rng.randrange(1 << nx) if nx else 0)
+
+
+def test_cyclotomic_out_c_lazy_sum():
+    """cyc_outc (csrc/bn_fq.cuh): 3 (S +- m' - 10 m) - 2 z in one lazily accumulated sum, against Python integers (extremes first)."""
+    lib = hostsim.lib()
+    big = o.Q - 1
+    cases = [(big, 0, big, 0), (0, big, 0, big), (big, big, big, big), (0, 0, 0, 0), (big, 0, 0, big), (0, big, big, 0)]
+    cases += [(rfq(), rfq(), rfq(), rfq()) for _ in range(3000)]
+    n = len(cases)
+    arr = [np.frombuffer(b"".join(int(c_[k]).to_bytes(32, "little") for c_ in cases), dtype=np.uint8).copy() for k in range(4)]
+    for plus in (0, 1):
+        out = np.zeros(32 * n, np.uint8)
+        lib.hs_cyc_outc(_p(arr[0]), _p(arr[1]), _p(arr[2]), ctypes.c_int(plus), _p(arr[3]), _p(out), ctypes.c_size_t(n))
+        for i, (s_, m_, mx_, z_) in enumerate(cases):
+            exp = (3 * (s_ + (mx_ if plus else -mx_) - 10 * m_) - 2 * z_) % o.Q
+            assert int.from_bytes(out[32 * i:32 * i + 32].tobytes(), "little") == exp, (i, plus)
