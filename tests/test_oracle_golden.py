@@ -187,3 +187,21 @@ def test_doubling_mask_matches_naf():
     bits += [0, 0]
     assert len(bits) == 87
     assert lo | (hi << 64) == sum(b << i for i, b in enumerate(bits))
+
+
+def test_bgcd_model_and_device_constants():
+    import os
+    """tools/bgcd_model.py (the Python model of fq_inv_bgcd, every bound of the C code asserted inside) converges to (0, 1) with
+    the inverse on extremes and random residues; the constants in csrc/bn_tower.cuh are the model's."""
+    import re
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, os.path.join(root, "tools"))
+    import bgcd_model as m
+    n, bad = m.self_test(400, seed=9)
+    assert n > 400 and bad == 0
+    src = open(os.path.join(root, "paritytech-bn_b200", "csrc", "bn_tower.cuh")).read()
+    assert int(re.search(r"#define BN_BGCD_K (\d+)", src).group(1)) == m.K
+    assert int(re.search(r"#define BN_BGCD_ROUNDS (\d+)", src).group(1)) == m.ROUNDS
+    assert int(re.search(r"#define BN_BGCD_NEGQINV 0x([0-9a-f]+)u", src).group(1), 16) == m.NEGQINV
+    assert m.K * m.ROUNDS >= 2 * 254 - 1

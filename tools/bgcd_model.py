@@ -1,3 +1,8 @@
+"""Python model of fq_inv_bgcd (csrc/bn_tower.cuh): binary extended Euclid in rounds of K = 30 steps on 64-bit approximations
+(low 30 bits under the top 34 bits of the common bit window), the steps collected in a 2 x 2 matrix applied once per round to the
+full-size values and, with an exact division by 2^K, to the cofactors modulo q.  Every bound the C code relies on is asserted
+here (exact divisibility, |f| + |g| <= 2^K, the quotient range of the cofactor update, the end state (0, 1) after 17 rounds).
+usage: bgcd_model.py [random cases]   (tests/test_hostsim.py runs the C code; tests/test_oracle_golden.py imports this model)"""
 import random, sys
 Q = 0x30644e72e131a029b85045b68181585d97816a916871ca8d3c208c16d87cfd47
 K = 30
@@ -62,15 +67,22 @@ def inv(y):
         a, b = na, nb
     return a, b, v
 
-rng = random.Random(1)
-vals = [1, 2, 3, Q - 1, Q - 2, (Q + 1) // 2, (Q - 1) // 2, 1 << 253, (1 << 253) + 1, (1 << 64) - 1, 1 << 64, (1 << 64) + 1, (1 << 128) - 1, 0xffffffff, 1 << 32]
-vals += [rng.randrange(1, Q) for _ in range(int(sys.argv[1]) if len(sys.argv) > 1 else 20000)]
-vals += [rng.randrange(1, 1 << rng.randrange(1, 254)) for _ in range(5000)]
-vals += [Q - rng.randrange(1, 1 << rng.randrange(1, 200)) for _ in range(5000)]
-bad = 0
-for y in vals:
-    a, b, v = inv(y)
-    if not (a == 0 and b == 1 and v * y % Q == 1):
-        bad += 1
-        print("FAIL", hex(y), a, b)
-print("checked", len(vals), "bad", bad)
+
+def self_test(n_random=20000, seed=1):
+    rng = random.Random(seed)
+    vals = [1, 2, 3, Q - 1, Q - 2, (Q + 1) // 2, (Q - 1) // 2, 1 << 253, (1 << 253) + 1, (1 << 64) - 1, 1 << 64, (1 << 64) + 1, (1 << 128) - 1, 0xffffffff, 1 << 32]
+    vals += [rng.randrange(1, Q) for _ in range(n_random)]
+    vals += [rng.randrange(1, 1 << rng.randrange(1, 254)) for _ in range(n_random // 4)]
+    vals += [Q - rng.randrange(1, 1 << rng.randrange(1, 200)) for _ in range(n_random // 4)]
+    bad = 0
+    for y in vals:
+        a, b, v = inv(y)
+        if not (a == 0 and b == 1 and v * y % Q == 1):
+            bad += 1
+    return len(vals), bad
+
+
+if __name__ == "__main__":
+    n, bad = self_test(int(sys.argv[1]) if len(sys.argv) > 1 else 20000)
+    print("checked", n, "bad", bad)
+    sys.exit(1 if bad else 0)
