@@ -205,3 +205,18 @@ def test_bgcd_model_and_device_constants():
     assert int(re.search(r"#define BN_BGCD_ROUNDS (\d+)", src).group(1)) == m.ROUNDS
     assert int(re.search(r"#define BN_BGCD_NEGQINV 0x([0-9a-f]+)u", src).group(1), 16) == m.NEGQINV
     assert m.K * m.ROUNDS >= 2 * 254 - 1
+
+
+def test_ptx_generator_simulates_and_committed_header_is_current(tmp_path):
+    """tools/gen_fq_ptx.py: every generated carry-chain routine (multiplication, wide product, both reductions, add / sub, 9a +- b,
+    the 9-limb reduction of the lazy sums, the wide add / sub pair and the borrow-free subtraction) is SIMULATED against Python
+    integers before it is printed; the header in the tree is exactly what the generator prints."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = tmp_path / "fq_ptx.cuh"
+    p = subprocess.run([sys.executable, os.path.join(root, "tools", "gen_fq_ptx.py"), "--out", str(out)], capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    assert "simulated OK" in p.stdout and "9-limb reductions" in p.stdout
+    assert out.read_text() == open(os.path.join(root, "paritytech-bn_b200", "csrc", "fq_ptx.cuh")).read()

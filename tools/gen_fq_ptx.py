@@ -647,11 +647,12 @@ def emit_function(P, inout=False):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--check", action="store_true", help="simulate only")
+    ap.add_argument("--out", default=None, help="write the header here instead of csrc/fq_ptx.cuh")
     args = ap.parse_args()
     check()
     if args.check:
         return 0
-    out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "paritytech-bn_b200", "csrc", "fq_ptx.cuh")
+    out = args.out or os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "paritytech-bn_b200", "csrc", "fq_ptx.cuh")
     with open(out, "w") as f:
         f.write("// GENERATED by tools/gen_fq_ptx.py -- do not edit.  Simulated against big-int ground truth at\n"
                 "// generation time.  8x32-bit-limb BN254 Fq arithmetic as single inline-PTX carry-chain blocks.\n"
