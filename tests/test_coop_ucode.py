@@ -75,3 +75,21 @@ def test_committed_header_is_up_to_date(tmp_path):
 def test_window_digits_reconstruct_u():
     d = g.wnaf4(o.BN_U)
     assert sum(x << i for i, x in enumerate(d)) == o.BN_U and all(x == 0 or (x % 2 and -7 <= x <= 7) for x in d)
+
+
+def test_tables_and_slot_files_fit_the_shared_memory_of_one_sm():
+    """The launch shapes of csrc/bn_coop.cuh (16 warps per block) and csrc/bn_coop4.cuh (4 groups per block) against the 227 KB a
+    block may use on sm_100a, from the generated sizes: a routine added to the generator must not silently break a launch."""
+    import re
+    hdr = open(os.path.join(ROOT, "paritytech-bn_b200", "csrc", "bn_coop_ucode.cuh")).read()
+    d = {k: int(v) for k, v in re.findall(r"#define (BN_COOP4?_[A-Z_0-9]+) (\d+)", hdr)}
+    slot_bytes = d["BN_COOP_NSLOTS"] * 64
+    seq_words = (d["BN_COOP_NSTEPS_SEQ"] * 160 + d["BN_COOP_NSTEPS_SEQ"] + d["BN_COOP_NTRACE"] + 3) & ~3
+    quad_words = (d["BN_COOP_NSTEPS"] * 160 + d["BN_COOP_NSTEPS"] + 2 * d["BN_COOP4_NTRACE"] + 3) & ~3
+    limit = 227 * 1024
+    assert seq_words * 4 + 16 * slot_bytes <= limit, (seq_words * 4, slot_bytes)
+    assert quad_words * 4 + 4 * slot_bytes <= limit
+    src = open(os.path.join(ROOT, "paritytech-bn_b200", "csrc", "bn_coop.cuh")).read()
+    src4 = open(os.path.join(ROOT, "paritytech-bn_b200", "csrc", "bn_coop4.cuh")).read()
+    assert "#define BN_COOP_MAX_WARPS 16" in src and "#define BN_COOP4_MAX_GROUPS 4" in src4
+    assert d["BN_COOP4_W_LANE0"] == 24 and d["BN_COOP_NSTEPS"] < 255          # 0xff is "no step" in the paired trace
