@@ -212,17 +212,43 @@ __device__ __noinline__ void s_prep2(const Fq2& ai, const Fq2& aj, const Fq2& bi
 // one output coefficient: t = Q - Va - Vb; kind 0: xi t + Vc, kind 1: t + xi Vc, kind 2: t + Vc; then minus (aa + bb) for
 // post = 1, minus (aa - bb) for post = 2 (the Fq12-level Karatsuba correction, operands in local memory); result to local memory
 __device__ __noinline__ void s_f6_out(Fq2& out, sp Q, sp Va, sp Vb, sp Vc, int kind, const Fq2& aa, const Fq2& bb, int post) {
+    if (kind != 2) {
+        // the outputs that carry a multiplication by xi: every component is ONE lazily accumulated 288-bit sum, reduced once
+        // (|sum| <= 33 q): kind 0  c0 = Vc0 + 9 X0 - X1, c1 = Vc1 + 9 X1 + X0 with X = Q - Va - Vb;  kind 1  c0 = X0 + 9 Vc0 - Vc1,
+        // c1 = X1 + 9 Vc1 + Vc0;  then minus (aa +- bb)
+        Acc9 x0, x1, t0, t1, v;
+        {
+            Fq2 a = s_ld(Q), b = s_ld(Va), c = s_ld(Vb);
+            acc9_set(x0, a.c0); acc9_subu(x0, b.c0); acc9_subu(x0, c.c0);
+            acc9_set(x1, a.c1); acc9_subu(x1, b.c1); acc9_subu(x1, c.c1);
+        }
+        Fq2 w = s_ld(Vc);
+        if (kind == 0) {
+            acc9_set(t0, w.c0); acc9_addv(t0, x0); acc9_shl<3>(v, x0); acc9_addv(t0, v); acc9_subv(t0, x1);
+            acc9_set(t1, w.c1); acc9_addv(t1, x1); acc9_shl<3>(v, x1); acc9_addv(t1, v); acc9_addv(t1, x0);
+        } else {
+            Acc9 u;
+            t0 = x0; acc9_addu(t0, w.c0); acc9_set(u, w.c0); acc9_shl<3>(v, u); acc9_addv(t0, v); acc9_subu(t0, w.c1);
+            t1 = x1; acc9_addu(t1, w.c1); acc9_set(u, w.c1); acc9_shl<3>(v, u); acc9_addv(t1, v); acc9_addu(t1, w.c0);
+        }
+        if (post) {
+            Fq2 x = fq2_ld(aa), y = fq2_ld(bb);
+            acc9_subu(t0, x.c0); acc9_subu(t1, x.c1);
+            if (post == 1) { acc9_subu(t0, y.c0); acc9_subu(t1, y.c1); }
+            else { acc9_addu(t0, y.c0); acc9_addu(t1, y.c1); }
+        }
+        Fq2 r;
+        acc9_reduce<true>(r.c0, t0);
+        acc9_reduce<true>(r.c1, t1);
+        fq2_st(out, r);
+        return;
+    }
+    // kind 2 (no multiplication by xi): three to five canonical operations are cheaper than a lazy sum and its reduction
     Fq2 t = s_ld(Q), v = s_ld(Va), w = s_ld(Vc), x, y;
     fq_sub(t.c0, t.c0, v.c0); fq_sub(t.c1, t.c1, v.c1);
     v = s_ld(Vb);
     fq_sub(t.c0, t.c0, v.c0); fq_sub(t.c1, t.c1, v.c1);
-    if (kind == 0) { x = t; y = w; } else { x = w; y = t; }
-    if (kind != 2) {
-        Fq2 n;
-        fq_lin9<true>(n.c0, x.c0, x.c1);
-        fq_lin9<false>(n.c1, x.c1, x.c0);
-        x = n;
-    }
+    x = w; y = t;
     fq_add(t.c0, x.c0, y.c0); fq_add(t.c1, x.c1, y.c1);
     if (post) {
         x = fq2_ld(aa); y = fq2_ld(bb);
